@@ -1,0 +1,97 @@
+"""ctypes binding of libcpe_b200.so (the C ABI declared in include/cpe.h).
+
+There is NO fallback: if the CUDA library is missing or a call fails, this raises.  torch is used only for
+device memory and streams (`tensor.data_ptr()`, `torch.cuda.current_stream().cuda_stream`).
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libcpe_b200.so")
+
+c_i32p = C.c_void_p
+c_f64p = C.c_void_p
+
+
+class CpeModel(C.Structure):
+    _fields_ = [
+        ("n_ineq", C.c_int32), ("n_blocks", C.c_int32), ("n_groups", C.c_int32), ("n_blk_items", C.c_int32),
+        ("chain_link", c_i32p), ("slot_of", c_i32p), ("eq_pairs", c_i32p), ("ineq_idx", c_i32p),
+        ("ineq_bounds", c_f64p), ("wq", c_f64p), ("meas_w", c_f64p), ("ind_idx", c_i32p), ("ind_pos", c_i32p),
+        ("blk_nodes", c_i32p), ("blk_id", c_i32p), ("blk_item_ptr", c_i32p), ("blk_items", c_i32p),
+        ("blk_eq_ptr", c_i32p), ("blk_eq_items", c_i32p), ("grp_ndep", c_i32p), ("grp_nnb", c_i32p),
+        ("grp_dep", c_i32p), ("grp_nb", c_i32p), ("grp_nbpos", c_i32p),
+    ]
+
+
+class CpeBatch(C.Structure):
+    _fields_ = [
+        ("S", C.c_int32), ("N", C.c_int32), ("C", C.c_int32), ("W", C.c_int32),
+        ("cam_model", C.c_int32), ("meas_is_f64", C.c_int32),
+        ("mu_eq", C.c_double), ("mu_in", C.c_double),
+        ("loss_a", C.c_double), ("loss_b", C.c_double), ("loss_c", C.c_double),
+        ("n_frames", c_i32p), ("h", c_f64p), ("meas", C.c_void_p), ("cams", c_f64p), ("chain_vec", c_f64p),
+        ("lam_eq", c_f64p), ("lam_in", c_f64p),
+    ]
+
+
+class CpeEvalOut(C.Structure):
+    _fields_ = [("frame_cost", c_f64p), ("pose", c_f64p), ("resid", c_f64p), ("c_eq", c_f64p), ("v_in", c_f64p),
+                ("jac", c_f64p)]
+
+
+class CpeAssembleOut(C.Structure):
+    _fields_ = [("S", c_f64p), ("ghat", c_f64p), ("Y", c_f64p), ("y", c_f64p), ("g", c_f64p), ("diagH", c_f64p),
+                ("Hraw", c_f64p)]
+
+
+class CpeSolveIO(C.Structure):
+    _fields_ = [("Lfac", c_f64p), ("zbuf", c_f64p), ("delta_ind", c_f64p), ("status", c_i32p)]
+
+
+EXPORTS = {
+    "cpe_version": (C.c_int, []),
+    "cpe_eval_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpeBatch), c_f64p, C.POINTER(CpeEvalOut), C.c_void_p]),
+    "cpe_reduce_cost_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, C.c_void_p]),
+    "cpe_assemble_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpeBatch), c_f64p, c_f64p,
+                                   C.POINTER(CpeAssembleOut), C.c_void_p]),
+    "cpe_band_solve_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpeBatch), c_f64p, c_f64p,
+                                     C.POINTER(CpeSolveIO), C.c_void_p]),
+    "cpe_step_apply_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpeBatch), c_f64p, c_f64p,
+                                     C.POINTER(CpeAssembleOut), c_f64p, c_f64p, c_f64p, c_f64p, C.c_void_p]),
+    "cpe_step_accept_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p, c_f64p, c_f64p, c_i32p, c_i32p,
+                                      C.c_double, C.c_void_p]),
+    "cpe_update_multipliers_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p,
+                                             c_f64p, C.c_void_p]),
+    "cpe_eval_host_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpeBatch), C.c_void_p, C.c_void_p, c_f64p,
+                                    C.c_void_p, C.POINTER(CpeEvalOut), c_f64p, C.c_void_p, C.c_void_p, C.c_void_p]),
+}
+
+_lib = None
+
+
+class CpeError(RuntimeError):
+    pass
+
+
+def load():
+    """Load libcpe_b200.so and type its entry points.  Raises if the library is absent (no CPU fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise CpeError(f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                       "(nvcc, sm_100a). There is no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in EXPORTS.items():
+        fn = getattr(lib, name)          # AttributeError if the symbol is missing
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc, what):
+    if rc != 0:
+        kind = "argument error" if rc < 0 else "CUDA error"
+        raise CpeError(f"{what} failed: {kind} {rc}")

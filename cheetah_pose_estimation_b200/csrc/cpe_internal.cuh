@@ -1,0 +1,76 @@
+// cpe_internal.cuh -- device helpers shared by the kernels (projection, robust loss).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "cpe.h"
+
+namespace cpe {
+
+struct Proj {
+    double u, v;
+    double du[3], dv[3];   // d(u,v)/d(world point)
+};
+
+// Camera projection of one world point.  cam = fx fy cx cy D0..D3 R[9] t[3] mult.
+//   fisheye: reference acinoset_misc.py:1663-1679 (Kannala-Brandt, `r + 1e-12`, no skew)
+//   pinhole: reference acinoset_misc.py:1682-1696 (radial r^2, r^4, r^6 with D[0..2])
+template <bool DERIV>
+__device__ __forceinline__ void project_point(const double *X, const double *cam, int model, Proj &o) {
+    const double *R = cam + 8;
+    const double x = X[0] * R[0] + X[1] * R[1] + X[2] * R[2] + cam[17];
+    const double y = X[0] * R[3] + X[1] * R[4] + X[2] * R[5] + cam[18];
+    const double z = X[0] * R[6] + X[1] * R[7] + X[2] * R[8] + cam[19];
+    const double a = x / z, b = y / z;
+    const double r2 = a * a + b * b;
+    const double r = sqrt(r2);
+    double s, g = 0.0;
+    if (model == CPE_CAM_FISHEYE) {
+        const double th = atan(r);
+        const double t2 = th * th;
+        const double poly = 1.0 + t2 * (cam[4] + t2 * (cam[5] + t2 * (cam[6] + t2 * cam[7])));
+        const double thd = th * poly;
+        const double re = r + 1e-12;
+        s = thd / re;
+        if (DERIV) {
+            const double dpoly = 1.0 + t2 * (3.0 * cam[4] + t2 * (5.0 * cam[5] + t2 * (7.0 * cam[6] + t2 * 9.0 * cam[7])));
+            const double ds_dr = (dpoly / (1.0 + r2) * re - thd) / (re * re);
+            g = r > 0.0 ? ds_dr / r : 0.0;
+        }
+    } else {
+        s = 1.0 + r2 * (cam[4] + r2 * (cam[5] + r2 * cam[6]));
+        if (DERIV) g = 2.0 * cam[4] + r2 * (4.0 * cam[5] + 6.0 * r2 * cam[6]);
+    }
+    o.u = cam[0] * (a * s) + cam[2];
+    o.v = cam[1] * (b * s) + cam[3];
+    if (DERIV) {
+        const double iz = 1.0 / z;
+        const double xa = s + a * a * g, xb = a * b * g, yb = s + b * b * g;
+        // d(u)/d(Xc) and d(v)/d(Xc)
+        const double ux = cam[0] * xa * iz, uy = cam[0] * xb * iz, uz = -cam[0] * (xa * a + xb * b) * iz;
+        const double vx = cam[1] * xb * iz, vy = cam[1] * yb * iz, vz = -cam[1] * (xb * a + yb * b) * iz;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            o.du[j] = ux * R[j] + uy * R[3 + j] + uz * R[6 + j];
+            o.dv[j] = vx * R[j] + vy * R[3 + j] + vz * R[6 + j];
+        }
+    }
+}
+
+// Redescending loss of the reference (acinoset_misc.py:2001-2015) at magnitude E = |err| and its derivative
+// d rho / dE.  sigma(E - s) = 1 / (1 + exp(s) exp(-E)) needs a single exp per residual.
+__device__ __forceinline__ void redescending(double E, double a, double b, double c, double ea, double eb, double ec,
+                                             double &rho, double &drho) {
+    const double t = exp(-E);
+    const double sa = 1.0 / (1.0 + t * ea), sb = 1.0 / (1.0 + t * eb), sc = 1.0 / (1.0 + t * ec);
+    const double da = sa * (1.0 - sa), db = sb * (1.0 - sb), dc = sc * (1.0 - sc);
+    const double cb = c - b;
+    const double p2 = a * E - 0.5 * a * a;
+    const double q = (c - E) / cb;
+    const double p3 = a * b - 0.5 * a * a + (0.5 * a * cb) * (1.0 - q * q);
+    const double k4 = a * b - 0.5 * a * a + 0.5 * a * cb;
+    rho = (1.0 - sa) * 0.5 * E * E + (sa - sb) * p2 + (sb - sc) * p3 + sc * k4;
+    drho = -da * 0.5 * E * E + (1.0 - sa) * E + (da - db) * p2 + (sa - sb) * a + (db - dc) * p3 +
+           (sb - sc) * a * (c - E) / cb + dc * k4;
+}
+
+}  // namespace cpe

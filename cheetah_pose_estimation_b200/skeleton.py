@@ -1,0 +1,304 @@
+"""Static description of the 17-link cheetah skeleton and the tables the CUDA kernels consume.
+
+Host-side only (numpy, no arithmetic of the hot path): link parameters, marker chains, joint pairs,
+inequality rows, sigma tables, and the sparsity tables of the per-frame Gauss-Newton Hessian.
+
+Reference sources (paths under the reference repo):
+  link order / topology      cheetah.py:19-200 (absolute-orientation branch), links.py:496-519
+  marker offsets             acinoset_misc.py:1581-1659
+  joint equalities           links.py:552-586 ; cheetah.py:71-72,101,160-161
+  inequalities               cheetah.py:306-352 ; links.py:602-605,636-639
+  sigma / process noise      acinoset_misc.py:1760-1911 ; mask :1699-1757
+  markers / DLC columns      acinoset_misc.py:1914-1998
+  animal parameters          cheetah_params.py
+"""
+import math
+
+import numpy as np
+
+N_MARKERS, N_LINKS, N_COORDS, MAX_CHAIN, N_NODES = 24, 17, 54, 5, 18
+N_IND, N_DEP, N_EQ = 28, 26, 26
+GRP_MAX_DEP, GRP_MAX_NB = 6, 12
+CAM_STRIDE = 24
+
+MARKERS = [
+    "nose", "r_eye", "l_eye", "neck_base", "spine", "tail_base", "tail1", "tail2",
+    "r_shoulder", "r_front_knee", "r_front_ankle", "r_front_paw",
+    "l_shoulder", "l_front_knee", "l_front_ankle", "l_front_paw",
+    "r_hip", "r_back_knee", "r_back_ankle", "r_back_paw",
+    "l_hip", "l_back_knee", "l_back_ankle", "l_back_paw",
+]
+LINKS = ["base", "bodyF", "neck", "tail0", "tail1", "UFL", "LFL", "HFL", "UFR", "LFR", "HFR",
+         "UBL", "LBL", "UBR", "LBR", "HBL", "HBR"]
+(BASE, BODYF, NECK, TAIL0, TAIL1, UFL, LFL, HFL, UFR, LFR, HFR, UBL, LBL, UBR, LBR, HBL, HBR) = range(17)
+
+# DLC body-part column of every marker (acinoset_misc.py:1943-1969), in MARKERS order
+DLC_INDEX = [23, 0, 1, 24, 6, 22, 11, 12, 2, 3, 4, 5, 13, 14, 15, 16, 7, 8, 9, 10, 17, 18, 19, 20]
+# pairwise graph (acinoset_misc.py:1972-1998), in MARKERS order
+PAIRWISE = [[0, 1], [23, 1], [23, 0], [6, 23], [22, 24], [6, 11], [6, 22], [11, 22],
+            [3, 24], [2, 4], [2, 3], [3, 4], [14, 24], [13, 15], [13, 14], [14, 15],
+            [8, 22], [7, 9], [7, 8], [8, 9], [18, 22], [17, 19], [17, 18], [18, 19]]
+
+_SIGMA = np.array([
+    [1.2, 1.24, 1.18, 2.08, 2.04, 2.52, 2.73, 1.83, 3.47, 2.75, 2.69, 2.24,
+     3.4, 2.91, 2.85, 2.27, 3.26, 2.76, 2.33, 2.4, 3.53, 2.69, 2.49, 2.34],
+    [2.71, 3.06, 2.99, 4.07, 5.53, 4.67, 6.05, 5.6, 5.01, 5.11, 5.24, 4.85,
+     5.18, 5.28, 5.5, 4.9, 4.7, 4.7, 5.21, 5.11, 5.1, 5.27, 5.75, 5.44],
+    [2.8, 3.24, 3.42, 3.8, 4.4, 5.43, 5.22, 7.29, 8.19, 6.5, 5.9, 6.18,
+     8.83, 6.52, 6.22, 6.34, 6.8, 6.12, 5.37, 5.98, 7.83, 6.44, 6.1, 6.38]])
+_Q_STD = np.array([4, 7, 5, 13, 9, 26, 10, 53, 34, 32, 18, 12, 0, 90, 43, 0, 118, 51,
+                   0, 247, 0, 0, 186, 0, 0, 91, 0, 0, 194, 0, 0, 164, 0, 0, 91, 0,
+                   0, 295, 0, 0, 243, 0, 0, 334, 0, 0, 149, 0, 0, 132, 0, 0, 132, 0], dtype=float)
+
+
+def measurement_weights(kinetic_dataset=False):
+    """1/R_pw[w][l] with R_pw = 2 * sigma (acinoset_misc.py:1850, :231); kinetic dataset: R_pw = 7 (:187-188)."""
+    r = _SIGMA * 2.0
+    if kinetic_dataset:
+        r = np.full_like(r, 7.0)
+    return 1.0 / r
+
+
+def motion_weights():
+    """1/Q_p (Q already squared) where Q_p != 0 else 0 (acinoset_misc.py:234, :1908)."""
+    q2 = _Q_STD ** 2
+    w = np.zeros(54)
+    w[q2 != 0] = 1.0 / q2[q2 != 0]
+    return w
+
+
+def independent_coords():
+    return np.nonzero(_Q_STD != 0)[0].astype(np.int32)
+
+
+_TWO_PI = 2 * math.pi
+_ANIMALS = {
+    "arabia": dict(body_B=(0.252, 0.54 / _TWO_PI, 18.0), body_F=(0.378, 0.673 / _TWO_PI, 9.0),
+                   neck=(0.308, 0.1, 0.4), tail0=(0.3, 0.0255, 0.4), tail1=(0.3, 0.0255, 0.2),
+                   front=((0.242, 0.012, 0.162), (0.232, 0.008, 0.067), (0.1, 0.008, 0.02)),
+                   back=((0.267, 0.012, 0.189), (0.278, 0.01, 0.156), (0.17, 0.01, 0.06))),
+    "shiraz": dict(body_B=(0.252, 0.54 / _TWO_PI, 19.0), body_F=(0.378, 0.673 / _TWO_PI, 13.0),
+                   neck=(0.308, 0.1, 0.4), tail0=(0.3, 0.0255, 0.4), tail1=(0.3, 0.0255, 0.2),
+                   front=((0.242, 0.012, 0.162), (0.232, 0.008, 0.067), (0.12, 0.008, 0.02)),
+                   back=((0.267, 0.012, 0.189), (0.278, 0.01, 0.156), (0.17, 0.01, 0.06))),
+    "phantom": dict(body_B=(0.296, 0.594 / _TWO_PI, 18.6), body_F=(0.444, 0.717 / _TWO_PI, 12.4),
+                    neck=(0.31, 0.1, 0.4), tail0=(0.28, 0.0255, 0.4), tail1=(0.36, 0.0255, 0.2),
+                    front=((0.26, 0.012, 0.2052), (0.27, 0.005, 0.0816), (0.125, 0.008, 0.02)),
+                    back=((0.26, 0.012, 0.252), (0.29, 0.01, 0.12), (0.265, 0.01, 0.072))),
+    "jules": dict(body_B=(0.296, 0.594 / _TWO_PI, 21.0), body_F=(0.444, 0.717 / _TWO_PI, 14.0),
+                  neck=(0.35, 0.1, 0.4), tail0=(0.28, 0.0255, 0.4), tail1=(0.36, 0.0255, 0.2),
+                  front=((0.24, 0.012, 0.2052), (0.28, 0.005, 0.0816), (0.155, 0.008, 0.02)),
+                  back=((0.27, 0.012, 0.252), (0.33, 0.01, 0.12), (0.245, 0.01, 0.072))),
+    "acinoset": dict(body_B=(0.37, 0.594 / _TWO_PI, 28.0), body_F=(0.37, 0.717 / _TWO_PI, 14.0),
+                     neck=(0.308, 0.1, 0.4), tail0=(0.28, 0.0255, 0.4), tail1=(0.36, 0.0255, 0.2),
+                     front=((0.24, 0.012, 0.2052), (0.28, 0.005, 0.0816), (0.14, 0.008, 0.02)),
+                     back=((0.32, 0.012, 0.252), (0.25, 0.01, 0.12), (0.22, 0.01, 0.072))),
+}
+
+
+def animal(name):
+    """(length[17], radius[17], mass[17]) in LINKS order.  Unknown names map to "acinoset" (acinoset_opt.py:453-454)."""
+    p = _ANIMALS.get(name, _ANIMALS["acinoset"])
+    f, b = p["front"], p["back"]
+    rows = [p["body_B"], p["body_F"], p["neck"], p["tail0"], p["tail1"], f[0], f[1], f[2], f[0], f[1], f[2],
+            b[0], b[1], b[0], b[1], b[2], b[2]]
+    a = np.array(rows, dtype=float)
+    return a[:, 0].copy(), a[:, 1].copy(), a[:, 2].copy()
+
+
+def marker_chains(lengths, radii):
+    """(chain_link[24,5] int32 (-1 unused), chain_vec[24,5,3]): marker = xyz + sum R_link @ vec."""
+    L = np.asarray(lengths, float)
+    rad = np.asarray(radii, float)
+
+    def v(x=0.0, y=0.0, z=0.0):
+        return (x, y, z)
+
+    spine = [(BASE, v(-L[BASE] / 2))]
+    tail_base = [(BASE, v(L[BASE] / 2))]
+    neck_base = spine + [(BODYF, v(-L[BODYF]))]
+    ch = [neck_base + [(NECK, v(-L[NECK] - 0.055, 0, -0.055))],
+          neck_base + [(NECK, v(-L[NECK], 0.045, 0))],
+          neck_base + [(NECK, v(-L[NECK], -0.045, 0))],
+          neck_base, spine, tail_base,
+          tail_base + [(TAIL0, v(L[TAIL0]))],
+          tail_base + [(TAIL0, v(L[TAIL0])), (TAIL1, v(L[TAIL1]))]]
+    for front, right, U, Lo, H in ((True, True, UFR, LFR, HFR), (True, False, UFL, LFL, HFL),
+                                   (False, True, UBR, LBR, HBR), (False, False, UBL, LBL, HBL)):
+        sy = 1.0 if right else -1.0
+        if front:
+            marker = spine + [(BODYF, v(-L[BODYF] + 0.06, sy * 0.075, -0.15))]
+            start = spine + [(BODYF, v(-L[BODYF] / 2 - L[BODYF] / 2, sy * rad[BODYF], 0))]
+        else:
+            marker = [(BASE, v(L[BASE] / 2 - 0.06, sy * 0.06, -0.1))]
+            start = [(BASE, v(L[BASE] / 2, sy * rad[BASE], 0))]
+        knee = start + [(U, v(0, 0, -L[U]))]
+        ankle = knee + [(Lo, v(0, 0, -L[Lo]))]
+        paw = ankle + [(H, v(0, 0, -L[H]))]
+        ch += [marker, knee, ankle, paw]
+    link = -np.ones((N_MARKERS, MAX_CHAIN), dtype=np.int32)
+    vec = np.zeros((N_MARKERS, MAX_CHAIN, 3))
+    for l, c in enumerate(ch):
+        for j, (li, vv) in enumerate(c):
+            link[l, j] = li
+            vec[l, j] = vv
+    return link, vec
+
+
+def joint_pairs():
+    """[26,4] (link_a, link_b, axis_a, axis_b): (R_a e_axis_a) . (R_b e_axis_b) = 0."""
+    pairs = [(BASE, TAIL0, 1, 2), (TAIL0, TAIL1, 1, 2)]
+    for body, U, Lo, H in ((BODYF, UFL, LFL, HFL), (BODYF, UFR, LFR, HFR), (BASE, UBL, LBL, HBL), (BASE, UBR, LBR, HBR)):
+        for a, b in ((body, U), (U, Lo), (Lo, H)):
+            pairs += [(a, b, 1, 0), (a, b, 1, 2)]
+    return np.array(pairs, dtype=np.int32)
+
+
+def inequality_rows(kinetic_dataset=False):
+    """(idx[n,2] int32, bounds[n,2]): lo <= q[idx0] - q[idx1] <= up (idx1 = -1: none)."""
+    PHI, TH, PSI = 0, 1, 2
+    pi = math.pi
+
+    def c(link, a):
+        return 3 + 3 * link + a
+
+    small = kinetic_dataset
+    rows = [
+        (c(NECK, PSI), c(BODYF, PSI), *((-0.05, 0.05) if small else (-pi / 6, pi / 6))),
+        (c(NECK, PHI), c(BODYF, PHI), *((-0.05, 0.05) if small else (-pi / 6, pi / 6))),
+        (c(BASE, PHI), -1, *((-0.05, 0.05) if small else (-pi / 6, pi / 6))),
+        (c(BODYF, PSI), c(BASE, PSI), *((-0.1, 0.1) if small else (-pi / 6, pi / 6))),
+        (c(BODYF, PHI), c(BASE, PHI), *((-0.1, 0.1) if small else (-pi / 6, pi / 6))),
+        (c(BASE, PSI), c(TAIL0, PSI), *((-0.1, 0.1) if small else (-pi / 1.5, pi / 1.5))),
+        (c(NECK, TH), c(BODYF, TH), -pi / 6, pi / 6),
+        (c(BODYF, TH), c(BASE, TH), -pi / 6, pi / 6),
+        (c(BASE, TH), c(TAIL0, TH), -pi / 1.5, pi / 1.5),
+        (c(TAIL0, TH), c(TAIL1, TH), -pi / 1.5, pi / 1.5),
+        (c(TAIL0, PSI), c(TAIL1, PSI), -pi / 1.5, pi / 1.5),
+    ]
+    for body, U, Lo, H, back in ((BODYF, UFL, LFL, HFL, False), (BODYF, UFR, LFR, HFR, False),
+                                 (BASE, UBL, LBL, HBL, True), (BASE, UBR, LBR, HBR, True)):
+        rows.append((c(body, TH), c(U, TH), -0.75 * pi, 0.75 * pi))
+        rows.append((c(U, TH), c(Lo, TH), *((0.0, pi) if back else (-pi, 0.0))))
+        rows.append((c(Lo, TH), c(H, TH), *((-0.75 * pi, 0.0) if back else (-pi / 4, 0.75 * pi))))
+    rows.append((2, -1, 0.0, 100.0))      # base z >= 0 (links.py:636-639), upper = the +-100 box (links.py:602)
+    idx = np.array([[r[0], r[1]] for r in rows], dtype=np.int32)
+    bounds = np.array([[r[2], r[3]] for r in rows], dtype=float)
+    return idx, bounds
+
+
+def relative_matrix():
+    """T[54,54]: get_relative_angles(q) = T @ q (acinoset_misc.py:487-528)."""
+    parent = {BODYF: BASE, NECK: BODYF, TAIL0: BASE, TAIL1: TAIL0, UFR: BODYF, UFL: BODYF, UBR: BASE, UBL: BASE,
+              LFR: UFR, LFL: UFL, LBR: UBR, LBL: UBL, HFR: LFR, HFL: LFL, HBR: LBR, HBL: LBL}
+    T = np.zeros((54, 54))
+    T[:6, :6] = np.eye(6)
+    for link in range(1, 17):
+        s = 1.0 if link in (BODYF, NECK) else -1.0
+        for a in range(3):
+            T[3 + 3 * link + a, 3 + 3 * link + a] = s
+            T[3 + 3 * link + a, 3 + 3 * parent[link] + a] = -s
+    return T
+
+
+def build_tables(kinetic_dataset=False):
+    """All static integer/float tables of `cpe_model` (include/cpe.h) as a dict of numpy arrays."""
+    lengths, radii, _ = animal("jules")                      # topology only
+    chain_link, _ = marker_chains(lengths, radii)
+    slot_of = -np.ones((N_MARKERS, N_NODES), dtype=np.int32)
+    slot_of[:, 0] = 0
+    for l in range(N_MARKERS):
+        for j in range(MAX_CHAIN):
+            if chain_link[l, j] >= 0:
+                slot_of[l, chain_link[l, j] + 1] = j + 1
+    eq = joint_pairs()
+    ineq_idx, ineq_bounds = inequality_rows(kinetic_dataset)
+    # block pattern: node pairs co-occurring in a marker chain
+    present = np.zeros((N_NODES, N_NODES), dtype=bool)
+    for l in range(N_MARKERS):
+        nodes = np.nonzero(slot_of[l] >= 0)[0]
+        for a in nodes:
+            for b in nodes:
+                present[a, b] = True
+    for (a, b, _, _) in eq:
+        assert present[a + 1, b + 1], "joint pair outside the marker-chain pattern"
+    for (ip, im) in ineq_idx:
+        if im >= 0:
+            assert present[ip // 3, im // 3]
+    blk_nodes, blk_id = [], -np.ones((N_NODES, N_NODES), dtype=np.int32)
+    for i in range(N_NODES):
+        for j in range(i + 1):
+            if present[i, j]:
+                blk_id[i, j] = len(blk_nodes)
+                blk_nodes.append((i, j))
+    blk_item_ptr, blk_items, blk_eq_ptr, blk_eq_items = [0], [], [0], []
+    for (i, j) in blk_nodes:
+        for l in range(N_MARKERS):
+            if slot_of[l, i] >= 0:
+                assert slot_of[l, j] >= 0, "chain pattern is not a tree"
+                blk_items.append(l)
+        blk_item_ptr.append(len(blk_items))
+        for k, (a, b, _, _) in enumerate(eq):
+            sides = {a + 1: 0, b + 1: 1}
+            if i in sides and j in sides:
+                blk_eq_items.append(k * 4 + sides[i] * 2 + sides[j])
+        blk_eq_ptr.append(len(blk_eq_items))
+    ind = independent_coords()
+    ind_pos = -np.ones(54, dtype=np.int32)
+    ind_pos[ind] = np.arange(len(ind))
+    dep = np.array([p for p in range(54) if ind_pos[p] < 0], dtype=np.int32)
+    # elimination groups = connected components of the dependent coordinates in the block pattern
+    comp = {int(p): int(p) for p in dep}
+
+    def find(x):
+        while comp[x] != x:
+            comp[x] = comp[comp[x]]
+            x = comp[x]
+        return x
+
+    for a in dep:
+        for b in dep:
+            if a < b and present[a // 3, b // 3]:
+                comp[find(int(a))] = find(int(b))
+    groups = {}
+    for p in dep:
+        groups.setdefault(find(int(p)), []).append(int(p))
+    glist = sorted(groups.values(), key=lambda g: g[0])
+    n_groups = len(glist)
+    grp_ndep = np.zeros(n_groups, dtype=np.int32)
+    grp_nnb = np.zeros(n_groups, dtype=np.int32)
+    grp_dep = np.zeros((n_groups, GRP_MAX_DEP), dtype=np.int32)
+    grp_nb = np.zeros((n_groups, GRP_MAX_NB), dtype=np.int32)
+    grp_nbpos = -np.ones((n_groups, N_IND), dtype=np.int32)
+    for g, deps in enumerate(glist):
+        assert len(deps) <= GRP_MAX_DEP
+        nbs = [int(p) for p in ind if any(present[p // 3, d // 3] for d in deps)]
+        assert len(nbs) <= GRP_MAX_NB, (deps, nbs)
+        grp_ndep[g], grp_nnb[g] = len(deps), len(nbs)
+        grp_dep[g, :len(deps)] = deps
+        grp_nb[g, :len(nbs)] = nbs
+        for j, p in enumerate(nbs):
+            grp_nbpos[g, ind_pos[p]] = j
+    return dict(
+        chain_link=chain_link.reshape(-1), slot_of=slot_of.reshape(-1), eq_pairs=eq.reshape(-1),
+        ineq_idx=ineq_idx.reshape(-1), ineq_bounds=ineq_bounds.reshape(-1), wq=motion_weights(),
+        meas_w=measurement_weights(kinetic_dataset).reshape(-1), ind_idx=ind, ind_pos=ind_pos,
+        blk_nodes=np.array(blk_nodes, dtype=np.int32).reshape(-1), blk_id=blk_id.reshape(-1),
+        blk_item_ptr=np.array(blk_item_ptr, dtype=np.int32), blk_items=np.array(blk_items, dtype=np.int32),
+        blk_eq_ptr=np.array(blk_eq_ptr, dtype=np.int32), blk_eq_items=np.array(blk_eq_items, dtype=np.int32),
+        grp_ndep=grp_ndep, grp_nnb=grp_nnb, grp_dep=grp_dep.reshape(-1), grp_nb=grp_nb.reshape(-1),
+        grp_nbpos=grp_nbpos.reshape(-1), dep_idx=dep,
+        n_ineq=len(ineq_idx), n_blocks=len(blk_nodes), n_groups=n_groups, n_blk_items=len(blk_items))
+
+
+def pack_camera(K, D, R, t, mult=1.0):
+    """One CAM_STRIDE-double camera record: fx fy cx cy D0..D3 R[9] t[3] mult pad[3]."""
+    K = np.asarray(K, float)
+    D = np.asarray(D, float).reshape(-1)
+    cam = np.zeros(CAM_STRIDE)
+    cam[0], cam[1], cam[2], cam[3] = K[0, 0], K[1, 1], K[0, 2], K[1, 2]
+    cam[4:4 + min(4, D.size)] = D[:4]
+    cam[8:17] = np.asarray(R, float).reshape(9)
+    cam[17:20] = np.asarray(t, float).reshape(3)
+    cam[20] = mult
+    return cam

@@ -1,0 +1,180 @@
+/* cpe.h -- C ABI of the B200-native cheetah trajectory-optimisation hot path (libcpe_b200.so).
+ *
+ * The reference (zicodasilva/cheetah_pose_estimation) has NO FFI: its hot path is the Pyomo model it hands to the
+ * external `ipopt` executable.  This ABI is what a maintainer binds (ctypes) to replace that seam:
+ *
+ *   reference seam being replaced                                         entry point here
+ *   -------------------------------------------------------------------  ---------------------------------------
+ *   misc.get_pose_state position_funcs          acinoset_misc.py:1581-1659  cpe_eval_f64  (pose output)
+ *   misc.pt3d_to_2d_fisheye / pt3d_to_2d        acinoset_misc.py:1663-1696  cpe_eval_f64  (resid output)
+ *   create_camera_contraints `measurement` rows acinoset_misc.py:278-288    cpe_eval_f64  (resid = slack_meas)
+ *   measurement_cost + redescending_loss        acinoset_misc.py:459-484,2001-2015  cpe_eval_f64 (cost[0])
+ *   constant_acc_cost + implicit-Euler colloc.  acinoset_misc.py:639-677; collocation.py:58-68  cpe_eval_f64 (cost[1])
+ *   angle_constr equalities                     system.py:574-586; links.py:552-586  cpe_eval_f64 (c_eq, cost[2])
+ *   add_pyomo_constraints inequalities          cheetah.py:306-352; links.py:602-605,636-639  cpe_eval_f64 (v_in, cost[3])
+ *   ASL Jacobian / Hessian evaluation inside ipopt (utils.py:522-535)     cpe_eval_f64 (jac), cpe_assemble_f64
+ *   MA97 KKT factorisation inside ipopt (acinoset_opt.py:611-617)         cpe_band_solve_f64
+ *   ipopt step acceptance                                                 cpe_step_apply_f64 / cpe_step_accept_f64
+ *
+ * Conventions: plain `extern "C"`; every pointer inside the structs is a DEVICE pointer owned by the caller
+ * (contiguous, 16-byte aligned) unless its comment says "host"; nothing is allocated or freed inside; every call is
+ * asynchronous on `stream`; no global state, thread-safe per stream.  Return value: 0 = OK, <0 = argument error
+ * (CPE_E_*), >0 = cudaError_t of the launch.  Per-sequence solver status is written to device arrays.
+ *
+ * Index conventions: S sequences, N = frame stride (max frames), C cameras, L = 24 markers, W hypotheses per marker
+ * (1, or 3 with pairwise pseudo-measurements), P = 54 generalised coordinates in the reference's order
+ * (cheetah.py:197-198): base x,y,z,phi,theta,psi then 16 x (phi,theta,psi).
+ */
+#ifndef CPE_H_
+#define CPE_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CPE_VERSION 100          /* 0.1.0 */
+
+#define CPE_N_MARKERS 24
+#define CPE_N_LINKS 17
+#define CPE_N_COORDS 54
+#define CPE_MAX_CHAIN 5          /* links between the base origin and a marker */
+#define CPE_N_NODES 18           /* node 0 = base xyz, node 1+i = link i: coordinate p lives in node p/3 */
+#define CPE_N_IND 28             /* coordinates with a motion prior (Q_p != 0) */
+#define CPE_N_DEP 26             /* coordinates without (eliminated per frame)  */
+#define CPE_N_EQ 26              /* joint equalities per frame */
+#define CPE_MAX_INEQ 32
+#define CPE_CAM_STRIDE 24        /* doubles per camera: fx fy cx cy D0..D3 R[9] t[3] mult pad[3] */
+#define CPE_MAX_CAMS 8
+#define CPE_GRP_MAX_DEP 6        /* elimination group: <= 6 dependent coords ... */
+#define CPE_GRP_MAX_NB 12        /* ... coupled to <= 12 independent coords */
+#define CPE_MAX_GROUPS 8
+#define CPE_COST_TERMS 4         /* measurement, model, al_eq, al_in */
+
+#define CPE_CAM_FISHEYE 0        /* acinoset_misc.py:1663-1679 */
+#define CPE_CAM_PINHOLE 1        /* acinoset_misc.py:1682-1696 */
+
+#define CPE_E_ARG (-1)
+#define CPE_E_DIM (-2)
+#define CPE_E_NULL (-3)
+
+/* Static skeleton tables (device pointers; built once on the host from the chain topology). */
+typedef struct cpe_model {
+    int32_t n_ineq;                 /* two-sided linear inequality rows per frame (<= CPE_MAX_INEQ) */
+    int32_t n_blocks;               /* nonzero lower-triangular 3x3 node-pair blocks of the frame Hessian */
+    int32_t n_groups;               /* elimination groups of dependent coordinates */
+    int32_t n_blk_items;
+    const int32_t *chain_link;      /* [24*5] link index or -1 */
+    const int32_t *slot_of;         /* [24*18] slot (0 = xyz, 1..5 = chain position) of node in marker chain, or -1 */
+    const int32_t *eq_pairs;        /* [26*4] link_a, link_b, axis_a, axis_b : (R_a e_axa).(R_b e_axb) = 0 */
+    const int32_t *ineq_idx;        /* [n_ineq*2] coord_plus, coord_minus (-1 = none): lo <= q[+] - q[-] <= up */
+    const double *ineq_bounds;      /* [n_ineq*2] lo, up */
+    const double *wq;               /* [54] motion weights 1/Q_p^2 (0 where Q_p = 0), acinoset_misc.py:234 */
+    const double *meas_w;           /* [3*24] 1/R_pw[w][l]  (acinoset_misc.py:231) */
+    const int32_t *ind_idx;         /* [28] coordinates with wq != 0 */
+    const int32_t *ind_pos;         /* [54] position of coord in ind_idx or -1 */
+    const int32_t *blk_nodes;       /* [n_blocks*2] row node >= col node */
+    const int32_t *blk_id;          /* [18*18] block id of (row node, col node) for row >= col, else -1 */
+    const int32_t *blk_item_ptr;    /* [n_blocks+1] */
+    const int32_t *blk_items;       /* marker indices whose chain contains the block's row node */
+    const int32_t *blk_eq_ptr;      /* [n_blocks+1] */
+    const int32_t *blk_eq_items;    /* eq index*4 + (row side)*2 + (col side); side 0 = link_a, 1 = link_b */
+    const int32_t *grp_ndep;        /* [n_groups] */
+    const int32_t *grp_nnb;         /* [n_groups] */
+    const int32_t *grp_dep;         /* [n_groups*6] coordinate indices */
+    const int32_t *grp_nb;          /* [n_groups*12] coordinate indices (independent) */
+    const int32_t *grp_nbpos;       /* [n_groups*28] position of ind coord r in the group's nb list, or -1 */
+} cpe_model;
+
+/* One batch of sequences. */
+typedef struct cpe_batch {
+    int32_t S, N, C, W;
+    int32_t cam_model;              /* CPE_CAM_FISHEYE / CPE_CAM_PINHOLE */
+    int32_t meas_is_f64;            /* 0: meas is float4 {u,v,gate,_}; 1: double4 */
+    double mu_eq, mu_in;            /* augmented-Lagrangian penalties */
+    double loss_a, loss_b, loss_c;  /* redescending loss break points (3, 10, 20) */
+    const int32_t *n_frames;        /* [S] frames used of each sequence (<= N) */
+    const double *h;                /* [S] time step 1/fps (acinoset_opt.py:483-487, 508) */
+    const void *meas;               /* [S,N,C,24,W] x 4 : u, v, gate (likelihood > thresh ? 1 : 0), unused */
+    const double *cams;             /* [S,C,24]  see CPE_CAM_STRIDE */
+    const double *chain_vec;        /* [S,24,5,3] body-frame vectors of the marker chains */
+    const double *lam_eq;           /* [S,N,26] multipliers (may be NULL = 0) */
+    const double *lam_in;           /* [S,N,n_ineq] (may be NULL = 0) */
+} cpe_batch;
+
+/* Optional outputs of cpe_eval (NULL = skip). */
+typedef struct cpe_eval_out {
+    double *frame_cost;             /* [S,N,4] per-frame partial sums (measurement, model, al_eq, al_in) */
+    double *pose;                   /* [S,N,24,3] marker positions */
+    double *resid;                  /* [S,N,C,24,W,2] slack = proj - meas (what the reference saves as meas_err) */
+    double *c_eq;                   /* [S,N,26] */
+    double *v_in;                   /* [S,N,n_ineq]  t - clamp(t, lo, up), t = d + lam/mu */
+    double *jac;                    /* [S,N,C,24,W,2,18] d(u,v)/d(chain coords: xyz, then 5 x 3 link angles) */
+} cpe_eval_out;
+
+/* Outputs of cpe_assemble: the per-frame reduced normal equations after Marquardt damping and elimination. */
+typedef struct cpe_assemble_out {
+    double *S;                      /* [S,N,28,28] Schur complement on the independent coordinates (no motion term) */
+    double *ghat;                   /* [S,N,28] reduced gradient (incl. motion gradient) */
+    double *Y;                      /* [S,N,n_groups,6,12] H_dd^-1 H_di per group */
+    double *y;                      /* [S,N,n_groups,6]    H_dd^-1 g_d */
+    double *g;                      /* [S,N,54] full gradient (incl. motion gradient) */
+    double *diagH;                  /* [S,N,54] diag of the undamped GN Hessian incl. motion diagonal */
+    double *Hraw;                   /* optional [S,N,54,54] dense undamped frame Hessian (tests / cpe_normal_eq) */
+} cpe_assemble_out;
+
+/* Workspace + outputs of the block-banded solve. */
+typedef struct cpe_solve_io {
+    double *Lfac;                   /* [S,N,4,28,28] workspace: L1,L2,L3 (unit-lower block factors) and P = D^-1 */
+    double *zbuf;                   /* [S,N,28] workspace */
+    double *delta_ind;              /* [S,N,28] out */
+    int32_t *status;                /* [S] out: 0 ok, 1 non-positive pivot encountered */
+} cpe_solve_io;
+
+int cpe_version(void);
+
+/* K1: FK + projection + robust loss (+ optional chain-sparse Jacobian). q[S,N,54]. */
+int cpe_eval_f64(const cpe_model *model, const cpe_batch *batch, const double *q, const cpe_eval_out *out,
+                 void *stream);
+
+/* Deterministic per-sequence reduction of frame_cost[S,N,4] -> cost[S,4] (fixed order). */
+int cpe_reduce_cost_f64(const cpe_batch *batch, const double *frame_cost, double *cost, void *stream);
+
+/* K2: fused residual + Jacobian + J^T J / J^T r accumulation + damping + per-frame elimination. damp[S]. */
+int cpe_assemble_f64(const cpe_model *model, const cpe_batch *batch, const double *q, const double *damp,
+                     const cpe_assemble_out *out, void *stream);
+
+/* K3: block-banded (block half-bandwidth 3, n = 28) LDL^T factor + solve of (blockdiag(S) + M) d = -ghat. */
+int cpe_band_solve_f64(const cpe_model *model, const cpe_batch *batch, const double *Sblk, const double *ghat,
+                       const cpe_solve_io *io, void *stream);
+
+/* K4: back-substitute the eliminated coordinates, form q_try = q + delta and the predicted reduction.
+ * frame_pred[S,N] = -1/2 g.delta + 1/2 damp sum diagH delta^2 (per frame partials). */
+int cpe_step_apply_f64(const cpe_model *model, const cpe_batch *batch, const double *q, const double *damp,
+                       const cpe_assemble_out *asm_out, const double *delta_ind, double *delta, double *q_try,
+                       double *frame_pred, void *stream);
+
+/* K5: per-sequence accept / reject with Nielsen damping update.
+ * state[4,S] (structure of arrays) = {merit F, damp, nu, last relative decrease (-1 = rejected)};
+ * counters[S,2] = {iterations, accepted}.  cost_try[S,4] from cpe_reduce_cost of q_try; q is overwritten by q_try
+ * where accepted.  active[S] (may be NULL): sequences with active == 0 are skipped; a sequence is switched off when
+ * an accepted step decreased the merit by less than ftol (relative) or its damping hit the ceiling. */
+int cpe_step_accept_f64(const cpe_batch *batch, const double *cost_try, const double *frame_pred, double *q,
+                        const double *q_try, double *state, int32_t *counters, int32_t *active, double ftol,
+                        void *stream);
+
+/* Augmented-Lagrangian multiplier update: lam_eq += mu_eq * c_eq ; lam_in = mu_in * v_in. */
+int cpe_update_multipliers_f64(const cpe_model *model, const cpe_batch *batch, const double *c_eq,
+                               const double *v_in, double *lam_eq, double *lam_in, void *stream);
+
+/* Host-buffer convenience wrapper used for the end-to-end metric: copies q and meas from (pinned) host memory,
+ * evaluates, and copies cost[S,4] (and resid if non-NULL) back.  d_* are caller-owned device staging buffers. */
+int cpe_eval_host_f64(const cpe_model *model, const cpe_batch *batch_dev, const double *h_q, const void *h_meas,
+                      double *d_q, void *d_meas, const cpe_eval_out *out_dev, double *d_cost, double *h_cost,
+                      double *h_resid, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CPE_H_ */

@@ -1,0 +1,241 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI of libcpe_b200.so) against the CPU oracle on the same
+seeded inputs and against the golden fixtures.  Tolerances: FP64 per-residual relative error <= 1e-9 (north star)."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-9
+
+
+def _rel(a, b):
+    return np.abs(a - b).max() / max(1.0, np.abs(b).max())
+
+
+@pytest.fixture(scope="module")
+def gpu():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.fail("GPU tests need a CUDA device")
+    from cheetah_pose_estimation_b200 import engine
+    return engine.Model("cuda:0")
+
+
+def _setup(model, S=3, N=12, C=6, seed=1):
+    import torch
+    from cheetah_pose_estimation_b200 import engine, synthetic
+    prob = synthetic.make_problem(S=S, N=N, C=C, seed=seed)
+    batch = prob.to_batch("cuda:0")
+    solver = engine.Solver(model, batch)
+    rng = np.random.default_rng(seed + 100)
+    q = prob.q_true + rng.normal(0, 0.05, prob.q_true.shape)
+    return prob, batch, solver, q, torch.as_tensor(q, device="cuda:0")
+
+
+def test_eval_matches_oracle(gpu):
+    import torch
+    from oracle import adapters, cost, kinematics
+    prob, batch, solver, q, qd = _setup(gpu)
+    rng = np.random.default_rng(5)
+    lam_eq = rng.normal(0, 3, (batch.S, batch.N, 26))
+    lam_in = rng.normal(0, 3, (batch.S, batch.N, gpu.n_ineq))
+    batch.lam_eq = torch.as_tensor(lam_eq, device="cuda:0")
+    batch.lam_in = torch.as_tensor(lam_in, device="cuda:0")
+    out = solver.evaluate(qd, pose=True, resid=True, constraints=True)
+    torch.cuda.synchronize()
+    for s in range(batch.S):
+        pb = adapters.from_synthetic(prob, s)
+        assert _rel(out["pose"][s].cpu().numpy(), kinematics.fk(q[s], pb.chain_link, pb.chain_vec)) < 1e-13
+        r = cost.residuals(pb, q[s])
+        got = out["resid"][s].cpu().numpy()
+        # per-residual relative error (floor 1 px on the denominator)
+        assert (np.abs(got - r) / np.maximum(np.abs(r), 1.0)).max() < RTOL
+        ref = cost.cost_terms(pb, q[s], lam_eq[s], lam_in[s])
+        assert np.allclose(out["cost"][s].cpu().numpy(), ref, rtol=RTOL, atol=1e-9)
+        _, _, c, v = cost.al_terms(pb, q[s], lam_eq[s], lam_in[s])
+        assert np.abs(out["c_eq"][s].cpu().numpy() - c).max() < 1e-13
+        assert np.abs(out["v_in"][s].cpu().numpy() - v).max() < 1e-12
+
+
+@pytest.mark.parametrize("fname,animal", [("clip_jules_run1_1.npz", "jules"), ("clip_phantom_run.npz", "phantom")])
+def test_eval_real_clip_known_answers(gpu, golden_dir, fname, animal):
+    """Shipped optimum of a real clip (cameras/detections recovered): residuals equal the saved
+    `meas_err`, the measurement cost equals the reference-function value, FK equals the saved `positions`."""
+    import torch
+    from cheetah_pose_estimation_b200 import engine, skeleton
+    g = np.load(os.path.join(golden_dir, fname))
+    N, C = g["detections"].shape[:2]
+    lengths, radii, _ = skeleton.animal(animal)
+    _, cvec = skeleton.marker_chains(lengths, radii)
+    meas = np.zeros((1, N, C, 24, 1, 4), np.float32)
+    meas[0, :, :, :, 0, 0:2] = g["detections"]
+    meas[..., 2] = 1.0
+    cams = np.zeros((1, C, 24))
+    cams[0, :, :20] = g["cams"]
+    cams[0, :, 20] = 1.0
+    batch = engine.Batch.from_numpy(meas, cams, cvec[None], [1.0 / float(g["fps"])])
+    solver = engine.Solver(gpu, batch, with_solver=False)
+    out = solver.evaluate(torch.as_tensor(g["q"][None].copy(), device="cuda:0"), pose=True, resid=True)
+    torch.cuda.synchronize()
+    assert np.abs(out["pose"][0].cpu().numpy() - g["positions"]).max() < 1e-13
+    assert np.abs(out["resid"][0, :, :, :, 0, :].cpu().numpy() - g["meas_err"][..., 0]).max() < 2e-4
+    cost = out["cost"][0].cpu().numpy()
+    assert abs(cost[0] - float(g["known_meas_cost_all_on"])) / float(g["known_meas_cost_all_on"]) < 1e-6
+    dd = g["ddq"][3:] - g["ddq"][2:-1]
+    from cheetah_pose_estimation_b200.skeleton import motion_weights
+    assert abs(cost[1] - float(np.sum(motion_weights() * dd * dd))) / cost[1] < 1e-8
+
+
+def test_jacobian_matches_oracle(gpu):
+    import torch
+    from oracle import adapters, cameras, kinematics
+    prob, batch, solver, q, qd = _setup(gpu, S=2, N=5, C=4)
+    out = solver.evaluate(qd, jac=True)
+    torch.cuda.synchronize()
+    for s in range(batch.S):
+        pb = adapters.from_synthetic(prob, s)
+        pose = kinematics.fk(q[s], pb.chain_link, pb.chain_vec)
+        G = kinematics.fk_jacobian(q[s], pb.chain_link, pb.chain_vec)                 # [N,24,3,54]
+        P = cameras.project_jacobian(pose[:, None], pb.cams[None, :, None, :])        # [N,C,24,2,3]
+        J = np.einsum("ncldi,nlia->nclda", P, G)                                      # dense [N,C,24,2,54]
+        got = out["jac"][s, :, :, :, 0].cpu().numpy()                                 # [N,C,24,2,18]
+        for l in range(24):
+            cols = [0, 1, 2]
+            for j in range(5):
+                li = pb.chain_link[l, j]
+                cols += [3 + 3 * li + a for a in range(3)] if li >= 0 else []
+            ref = J[:, :, l][..., cols]
+            assert _rel(got[:, :, l, :, :len(cols)], ref) < RTOL
+            assert np.abs(got[:, :, l, :, len(cols):]).max() == 0.0
+
+
+@pytest.mark.parametrize("with_mult", [False, True])
+def test_normal_equations_match_oracle(gpu, with_mult):
+    import torch
+    from oracle import adapters, cost
+    prob, batch, solver, q, qd = _setup(gpu, S=2, N=9, C=6, seed=7)
+    rng = np.random.default_rng(11)
+    if with_mult:
+        # push a few coordinates outside the inequality box so that PHR rows are active
+        q[:, :, 19] += 2.5
+        qd = torch.as_tensor(q, device="cuda:0")
+        lam_eq = rng.normal(0, 5, (batch.S, batch.N, 26))
+        lam_in = rng.normal(0, 5, (batch.S, batch.N, gpu.n_ineq))
+        batch.lam_eq = torch.as_tensor(lam_eq, device="cuda:0")
+        batch.lam_in = torch.as_tensor(lam_in, device="cuda:0")
+    else:
+        lam_eq = np.zeros((batch.S, batch.N, 26))
+        lam_in = np.zeros((batch.S, batch.N, gpu.n_ineq))
+    damp = torch.full((batch.S,), 1e-3, dtype=torch.float64, device="cuda:0")
+    Hraw = solver.assemble(qd, damp, raw=True)
+    torch.cuda.synchronize()
+    for s in range(batch.S):
+        pb = adapters.from_synthetic(prob, s)
+        H, g = cost.frame_normal_equations(pb, q[s], lam_eq[s], lam_in[s])
+        g = g + cost.motion_gradient(pb, q[s])
+        assert _rel(Hraw[s].cpu().numpy(), H) < RTOL
+        assert _rel(solver.g[s].cpu().numpy(), g) < RTOL
+
+
+def test_lm_step_matches_oracle(gpu):
+    import torch
+    from oracle import adapters, lm
+    prob, batch, solver, q, qd = _setup(gpu, S=2, N=14, C=6, seed=9)
+    damp = torch.tensor([1e-3, 5e-2], dtype=torch.float64, device="cuda:0")
+    delta, q_try, frame_pred = solver.lm_step(qd, damp)
+    torch.cuda.synchronize()
+    assert int(solver.status.sum()) == 0
+    for s in range(batch.S):
+        pb = adapters.from_synthetic(prob, s)
+        d_ref, pred_ref, _ = lm.lm_step(pb, q[s], np.zeros((batch.N, 26)), np.zeros((batch.N, 24)), float(damp[s]))
+        assert _rel(delta[s].cpu().numpy(), d_ref) < 1e-7
+        assert abs(float(frame_pred[s].sum()) - pred_ref) <= 1e-7 * abs(pred_ref)
+        assert _rel(q_try[s].cpu().numpy(), q[s] + d_ref) < 1e-7
+
+
+def test_ragged_frames_and_determinism(gpu):
+    """Padded frames are ignored, and a sequence's result does not depend on its batch neighbours."""
+    import torch
+    from cheetah_pose_estimation_b200 import engine
+    prob, batch, solver, q, qd = _setup(gpu, S=3, N=10, C=6, seed=13)
+    out_full = solver.evaluate(qd)["cost"].cpu().numpy().copy()
+    nf = np.array([10, 7, 4], np.int32)
+    batch2 = prob.to_batch("cuda:0")
+    batch2.n_frames = torch.as_tensor(nf, device="cuda:0")
+    s2 = engine.Solver(gpu, batch2)
+    c2 = s2.evaluate(qd)["cost"].cpu().numpy().copy()
+    assert np.array_equal(c2[0], out_full[0])
+    from oracle import adapters, cost, lm
+    prob.n_frames = nf
+    for s in (1, 2):
+        pb = adapters.from_synthetic(prob, s)
+        assert np.allclose(c2[s], cost.cost_terms(pb, q[s, :nf[s]]), rtol=RTOL, atol=1e-9)
+    damp = torch.full((3,), 1e-2, dtype=torch.float64, device="cuda:0")
+    delta, _, _ = s2.lm_step(qd, damp)
+    d = delta.cpu().numpy().copy()
+    for s in (1, 2):
+        pb = adapters.from_synthetic(prob, s)
+        d_ref, _, _ = lm.lm_step(pb, q[s, :nf[s]], np.zeros((nf[s], 26)), np.zeros((nf[s], 24)), 1e-2)
+        assert _rel(d[s, :nf[s]], d_ref) < 1e-7
+    # single-sequence batch gives bit-identical output for that sequence
+    one = engine.Batch(n_frames=batch2.n_frames[1:2].contiguous(), h=batch2.h[1:2].contiguous(), meas=batch2.meas[1:2].contiguous(),
+                       cams=batch2.cams[1:2].contiguous(), chain_vec=batch2.chain_vec[1:2].contiguous())
+    s1 = engine.Solver(gpu, one)
+    d1, _, _ = s1.lm_step(qd[1:2].contiguous(), damp[:1].contiguous())
+    assert np.array_equal(d1[0].cpu().numpy()[:nf[1]], d[1, :nf[1]])
+
+
+def test_pinhole_and_pairwise_layout(gpu):
+    """cam_model = pinhole (kinetic dataset) and W = 3 hypotheses per marker."""
+    import torch
+    from cheetah_pose_estimation_b200 import engine, synthetic
+    from oracle import adapters, cameras, cost
+    prob = synthetic.make_problem(S=1, N=6, C=4, seed=21)
+    rng = np.random.default_rng(3)
+    meas3 = np.repeat(prob.meas, 3, axis=4).copy()
+    meas3[..., 1, 0:2] += rng.normal(0, 3, meas3[..., 1, 0:2].shape).astype(np.float32)
+    meas3[..., 2, 0:2] += rng.normal(0, 5, meas3[..., 2, 0:2].shape).astype(np.float32)
+    cams = prob.cams.copy()
+    cams[:, :, 4:8] *= 0.2
+    cams[:, 2:, 20] = 0.6
+    batch = engine.Batch.from_numpy(meas3, cams, prob.chain_vec, prob.h, cam_model=engine.PINHOLE)
+    solver = engine.Solver(gpu, batch, with_solver=False)
+    q = prob.q_true + rng.normal(0, 0.03, prob.q_true.shape)
+    out = solver.evaluate(torch.as_tensor(q, device="cuda:0"), resid=True)
+    pb = adapters.problem_from_arrays(meas3[0], cams[0], prob.chain_link, prob.chain_vec[0], prob.h[0],
+                                      cam_model=cameras.PINHOLE)
+    r = cost.residuals(pb, q[0])
+    got = out["resid"][0].cpu().numpy()
+    assert (np.abs(got - r) / np.maximum(np.abs(r), 1.0)).max() < RTOL
+    assert np.allclose(out["cost"][0].cpu().numpy(), cost.cost_terms(pb, q[0]), rtol=RTOL, atol=1e-9)
+
+
+def test_solver_converges_like_oracle(gpu):
+    """Converged trajectories: final cost within 0.5 % of the oracle solver's and MPJPE within 1 mm of it."""
+    import torch
+    from oracle import adapters, kinematics, lm
+    from cheetah_pose_estimation_b200 import engine, synthetic
+    prob = synthetic.make_problem(S=2, N=30, C=6, seed=4)
+    batch = prob.to_batch("cuda:0")
+    solver = engine.Solver(gpu, batch)
+    res = solver.solve(torch.as_tensor(prob.q_init, device="cuda:0"), max_iter=30, n_outer=3)
+    torch.cuda.synchronize()
+    qg = res["q"].cpu().numpy()
+    for s in range(2):
+        pb = adapters.from_synthetic(prob, s)
+        ref = lm.solve(pb, prob.q_init[s], max_iter=30, n_outer=3)
+        f_ref = ref["cost_terms"][:2].sum()
+        f_gpu = res["cost"][s, :2].sum().item()
+        assert abs(f_gpu - f_ref) / f_ref < 5e-3, (f_gpu, f_ref)
+        pg = kinematics.fk(qg[s], pb.chain_link, pb.chain_vec)
+        pr = kinematics.fk(ref["q"], pb.chain_link, pb.chain_vec)
+        pt = kinematics.fk(prob.q_true[s], pb.chain_link, pb.chain_vec)
+
+        def mpjpe(a, b):
+            a = a - a.mean(axis=1, keepdims=True)
+            b = b - b.mean(axis=1, keepdims=True)
+            return 1000 * np.linalg.norm(a - b, axis=-1).mean()
+        assert abs(mpjpe(pg, pt) - mpjpe(pr, pt)) < 1.0, (mpjpe(pg, pt), mpjpe(pr, pt))
+        assert np.abs(res["c_eq"][s].cpu().numpy()).max() < 1e-4
