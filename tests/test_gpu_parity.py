@@ -108,7 +108,8 @@ def test_jacobian_matches_oracle(gpu):
                 cols += [3 + 3 * li + a for a in range(3)] if li >= 0 else []
             ref = J[:, :, l][..., cols]
             assert _rel(got[:, :, l, :, :len(cols)], ref) < RTOL
-            assert np.abs(got[:, :, l, :, len(cols):]).max() == 0.0
+            if len(cols) < 18:      # unused chain slots stay zero (paws use all 18)
+                assert np.abs(got[:, :, l, :, len(cols):]).max() == 0.0
 
 
 @pytest.mark.parametrize("with_mult", [False, True])
