@@ -1,0 +1,402 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200-native cheetah trajectory-optimisation hot path.
+
+Metric (BASELINE.json): residual+Jacobian frame.views/s (and, beside it, LM-solved sequences/s) on the synthetic
+sweep of SURVEY.md section 8d (C4: sequences x 500 frames x 6 cameras x 24 markers), next to the host-CPU path.
+
+A "step" = one pass of K1 (skeleton FK -> fisheye projection -> likelihood-weighted redescending loss -> residuals
++ chain-sparse Jacobian, FP64) over ALL of this rank's sequences, processed in waves that reuse one Jacobian
+buffer.  One frame.view = the 24 markers of one camera in one frame (48 residuals and their derivatives).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            # one rank per GPU (torchrun for N > 1)
+  python bench.py --impl reference ...                           # the CPU path (oracle port) on the host cores
+
+Prints ONE JSON line on rank 0 (see the keys in DESIGN.md section "Measurement").
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "residual+Jacobian frame.views/s"
+UNIT = "frame.views/s"
+# ALGORITHMIC bytes per frame.view of K1 in "evaluate" mode with FP64 residuals/Jacobian:
+# detections 24 x (u,v,w) f32 = 288 B, state 54 x 8 B / C=6 = 72 B, residuals 48 x 8 B = 384 B,
+# chain-sparse Jacobian 540 nnz x 8 B = 4320 B.
+ALGO_BYTES_PER_FV = 288 + 72 + 384 + 4320
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--seqs", type=int, default=4096, help="sequences PER GPU (weak scaling)")
+    ap.add_argument("--frames", type=int, default=500)
+    ap.add_argument("--cams", type=int, default=6)
+    ap.add_argument("--wave", type=int, default=512, help="sequences per launch (Jacobian buffer reuse)")
+    ap.add_argument("--lm-seqs", type=int, default=296, help="sequences of the LM-solve leg (0 = skip)")
+    ap.add_argument("--lm-iters", type=int, default=20)
+    ap.add_argument("--cpu-seqs", type=int, default=64, help="sequences of the cpu_baseline sample (0 = skip)")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--seed", type=int, default=0)
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return (f"C4 synthetic sweep: {a.seqs} sequences/GPU x {a.frames} frames x {a.cams} cams x 24 markers, "
+            f"W=1, fisheye, fps 120")
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# clocks (B200_PROFILING.md "clocks DURING the timed region")
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        self.p.wait()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, power, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2])); power.append(float(c[3]))
+            except ValueError:
+                continue
+            for n, v in zip(names, c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        self.f.close()
+        os.unlink(self.f.name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "power_w_max": max(power), "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# CPU path: the oracle port of the reference's cost/residual evaluation (+ analytic Jacobian), FP64 numpy.
+# This is the ONLY place bench.py touches oracle/ (cpu_baseline leg and --impl reference).
+def cpu_eval_sequence(args):
+    """Residuals, robust cost and the dense Jacobian d(u,v)/dq of one sequence; returns the measurement cost."""
+    import numpy as np
+    from oracle import adapters, cameras, cost, kinematics
+    meas, cams, chain_link, chain_vec, h, q = args
+    pb = adapters.problem_from_arrays(meas, cams, chain_link, chain_vec, h)
+    pose = kinematics.fk(q, pb.chain_link, pb.chain_vec)
+    uv = cameras.project(pose[:, None, :, :], pb.cams[None, :, None, :], pb.cam_model)
+    r = uv[:, :, :, None, :] - pb.meas[..., 0:2]
+    c = float(np.sum(cost.redescending_loss(pb.meas[..., 2:3] * r))) + cost.motion_cost(pb, q)
+    G = kinematics.fk_jacobian(q, pb.chain_link, pb.chain_vec)
+    P = cameras.project_jacobian(pose[:, None], pb.cams[None, :, None, :], pb.cam_model)
+    J = np.einsum("ncldi,nlia->nclda", P, G)
+    return c + 0.0 * float(J[0, 0, 0, 0, 0])
+
+
+def cpu_sample(a, S):
+    """Host copy of S sequences of the workload (numpy generator path; detections projected by the oracle)."""
+    from cheetah_pose_estimation_b200 import synthetic
+    from oracle import adapters
+    import numpy as np
+    prob = synthetic.make_problem(S=S, N=a.frames, C=a.cams, seed=a.seed, projector=adapters.projector,
+                                  n_unique=min(S, 8))
+    rng = np.random.default_rng(a.seed + 100)
+    q = prob.q_true + rng.normal(0, 0.05, prob.q_true.shape)
+    return [(prob.meas[s], prob.cams[s], prob.chain_link, prob.chain_vec[s], float(prob.h[s]), q[s]) for s in range(S)]
+
+
+def time_cpu(items, pool=None):
+    t0 = time.perf_counter()
+    if pool is None:
+        for it in items:
+            cpu_eval_sequence(it)
+    else:
+        pool.map(cpu_eval_sequence, items, chunksize=1)
+    return time.perf_counter() - t0
+
+
+def run_reference(a):
+    """--impl reference: the CPU path on all host cores; each step = a bounded sample of the workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import multiprocessing as mp
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    os.environ.setdefault("OMP_NUM_THREADS", "1")
+    S = max(cores, min(a.cpu_seqs, 2 * cores))
+    items = cpu_sample(a, S)
+    with mp.get_context("fork").Pool(cores) as pool:
+        for _ in range(a.warmup):
+            time_cpu(items[:cores], pool)
+        t = 0.0
+        for _ in range(a.steps):
+            t += time_cpu(items, pool)
+    fv = S * a.frames * a.cams * a.steps
+    val = fv / t
+    sample = f"{S} sequences x {a.frames} frames x {a.cams} cams per step (of {a.seqs}/GPU), {cores} processes"
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": 1e3 * t / a.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(a), "sample": sample},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "reference = Python+Pyomo/IPOPT, not installable here; timed: numpy FP64 oracle port of its "
+                    "FK/projection/redescending-cost functions + analytic Jacobian"}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+def run_b200(a):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: a CUDA device is required (the hot path has no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    import __graft_entry__ as ge
+    if rank == 0:
+        ge.build()
+    if world > 1:
+        dist.barrier()
+    from cheetah_pose_estimation_b200 import engine, synthetic
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    S, N, C = a.seqs, a.frames, a.cams
+    wave = min(a.wave, S)
+    model = engine.Model(dev)
+    batch, q_true, q_init = synthetic.make_device_problem(S, N, C, seed=a.seed + 1000 * rank, device=dev)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(a.seed + 100 + rank)
+    q = (q_true + 0.05 * torch.randn(q_true.shape, generator=gen, device=dev, dtype=torch.float64)).contiguous()
+    f64 = dict(dtype=torch.float64, device=dev)
+    bufs = {"jac": torch.empty(wave, N, C, 24, 1, 2, 18, **f64), "resid": torch.empty(wave, N, C, 24, 1, 2, **f64)}
+    waves = []
+    for s0 in range(0, S, wave):
+        s1 = min(S, s0 + wave)
+        bw = batch.window(s0, s1)
+        sv = engine.Solver(model, bw, with_solver=False)
+        n = s1 - s0
+        waves.append((sv, q[s0:s1], {"jac": bufs["jac"][:n], "resid": bufs["resid"][:n]}))
+    cost_all = torch.zeros(S, 4, **f64)
+
+    ev_pairs = []
+
+    def step(record=False):
+        for i, (sv, qw, bw) in enumerate(waves):
+            if record:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+            sv.evaluate_launch(qw, bw, cost_all[i * wave:i * wave + qw.shape[0]], record_mid=(e1 if record else None))
+            if record:
+                ev_pairs.append((e0, e1))
+
+    for _ in range(a.warmup):
+        step()
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t0.record()
+    for _ in range(a.steps):
+        step(record=True)
+    t1.record()
+    barrier()
+    ms = t0.elapsed_time(t1)
+    kern_ms = sum(e0.elapsed_time(e1) for e0, e1 in ev_pairs)
+    n_kern = len(ev_pairs)
+    launches = 2 * len(waves) * a.steps
+    cost_sum = cost_all.sum(dim=0)
+
+    # ---- end to end through the public host-buffer API ----------------------------------------------------------
+    e2e = None
+    if not a.no_e2e:
+        del bufs, waves
+        torch.cuda.empty_cache()
+        hev = engine.HostEvaluator(model, batch, S, wave)
+        h_q = torch.empty(q.shape, dtype=torch.float64).pin_memory()
+        h_q.copy_(q)
+        h_meas = torch.empty(batch.meas.shape, dtype=batch.meas.dtype).pin_memory()
+        h_meas.copy_(batch.meas)
+        for _ in range(max(1, min(a.warmup, 3))):
+            h_cost = hev(h_q, h_meas)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(a.steps):
+            h_cost = hev(h_q, h_meas)
+        e1.record()
+        barrier()
+        e2e_ms = e0.elapsed_time(e1)
+        assert torch.allclose(h_cost.sum(dim=0), cost_sum.cpu(), rtol=1e-12), "e2e result differs from resident run"
+        h2d, d2h = hev.bytes_per_call()
+        e2e = (e2e_ms, h2d, d2h)
+        del hev, h_q, h_meas
+        torch.cuda.empty_cache()
+    clk = clocks.stop() if rank == 0 else None
+    return dict(rank=rank, world=world, dev=dev, model=model, batch=batch, q=q, q_init=q_init, ms=ms, kern_ms=kern_ms,
+                n_kern=n_kern, launches=launches, e2e=e2e, clk=clk, cost_sum=cost_sum, wave=wave, barrier=barrier)
+
+
+def lm_leg(a, r):
+    """LM-solved sequences/s on a sub-batch (S_lm sequences of the same shape): the full augmented-Lagrangian /
+    LM loop (assemble -> block-banded LDL^T solve -> step -> accept) from the reference-style initial guess."""
+    import torch
+    from cheetah_pose_estimation_b200 import engine
+    S_lm = min(a.lm_seqs, r["batch"].S)
+    if S_lm <= 0:
+        return None
+    bw = r["batch"].window(0, S_lm)
+    solver = engine.Solver(r["model"], bw)
+    q0 = r["q_init"][:S_lm].contiguous()
+    solver.solve(q0, max_iter=2, n_outer=1)            # warm-up (lazy module load, allocator)
+    r["barrier"]()
+    l0 = solver.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    res = solver.solve(q0, max_iter=a.lm_iters, n_outer=3)
+    e1.record()
+    r["barrier"]()
+    ms = e0.elapsed_time(e1)
+    cnt = res["counters"].double().mean(dim=0).tolist()
+    ceq = float(res["c_eq"].abs().max())
+    f0 = None
+    return {"sequences": S_lm, "sequences_per_s": S_lm / (ms * 1e-3), "ms": ms,
+            "lockstep_iterations": res["lockstep_iterations"], "mean_iterations": cnt[0], "mean_accepted": cnt[1],
+            "launches": solver.launches - l0, "final_cost_mean": float(res["cost"][:, :2].sum(dim=1).mean()),
+            "max_abs_joint_violation": ceq, "failed_pivots": int(res["status"].sum()),
+            "ms_per_lockstep_iteration": ms / max(1, res["lockstep_iterations"]),
+            "settings": {"n_outer": 3, "max_iter": a.lm_iters, "ftol": 1e-6}}
+
+
+def cpu_baseline_leg(a):
+    if a.cpu_seqs <= 0:
+        return None
+    S = min(a.cpu_seqs, 16)
+    items = cpu_sample(a, S)
+    cpu_eval_sequence(items[0])
+    t = time_cpu(items)
+    reps = 1
+    while t < 10.0 and reps < 8:        # aim at >= 10 s of single-core work
+        t += time_cpu(items)
+        reps += 1
+    fv = S * a.frames * a.cams * reps
+    return {"value": fv / t, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": f"{S} sequences x {a.frames} frames x {a.cams} cams, {reps} pass(es), numpy FP64 oracle port "
+                      f"(residual + cost + dense Jacobian), 1 process; host has {os.cpu_count()} cores"}
+
+
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+        return
+    import torch
+    import torch.distributed as dist
+    r = run_b200(a)
+    world, rank = r["world"], r["rank"]
+    # max over ranks of the device-timed regions
+    t = torch.tensor([r["ms"], r["e2e"][0] if r["e2e"] else 0.0, r["kern_ms"] / max(1, r["n_kern"])],
+                     dtype=torch.float64, device=r["dev"])
+    stats = torch.cat([r["cost_sum"], torch.tensor([float(r["launches"])], dtype=torch.float64, device=r["dev"])])
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(stats, op=dist.ReduceOp.SUM)       # the path's only collective: final cost/statistics reduce
+    ms, e2e_ms, kern_ms = t.tolist()
+    lm = lm_leg(a, r)
+    if world > 1 and lm is not None:
+        v = torch.tensor([lm["ms"]], dtype=torch.float64, device=r["dev"])
+        dist.all_reduce(v, op=dist.ReduceOp.MAX)
+        lm["sequences"] *= world
+        lm["sequences_per_s"] = lm["sequences"] / (v.item() * 1e-3)
+        lm["ms"] = v.item()
+    if rank == 0:
+        fv_rank = a.seqs * a.frames * a.cams
+        fv_total = fv_rank * world
+        value = fv_total * a.steps / (ms * 1e-3)
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        fv_launch = r["wave"] * a.frames * a.cams
+        achieved = fv_launch * ALGO_BYTES_PER_FV / (kern_ms * 1e-3) / 1e9
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("frame_kernel_eval_jac")
+        except (OSError, ValueError):
+            pass
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+                "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f64", "data": "synthetic",
+                "config": {"workload": workload_name(a), "wave_sequences": r["wave"],
+                           "l2": "inputs+outputs per launch (>= 20 GB) exceed the 126 MB L2; no flush needed",
+                           "sharding": f"sequences, {a.seqs}/rank, no data-path collective"},
+                "gpu_launches": int(stats[4].item()),
+                "kernel": {"name": "frame_kernel<MODE_EVAL_JAC>", "avg_ms": kern_ms, "frame_views_per_launch": fv_launch},
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                             "frac": achieved / peak, "traffic": traffic,
+                             "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650",
+                             "algorithmic_bytes_per_frame_view": ALGO_BYTES_PER_FV},
+                "clocks": r["clk"], "cost_checksum": stats[:4].tolist()}
+        if r["e2e"]:
+            line["e2e"] = {"value": fv_total * a.steps / (e2e_ms * 1e-3), "unit": UNIT,
+                           "h2d_bytes_per_step": r["e2e"][1], "d2h_bytes_per_step": r["e2e"][2],
+                           "api": "engine.HostEvaluator -> cpe_eval_host_f64 (pinned host q + detections in, cost out)"}
+        if lm is not None:
+            line["lm"] = lm
+        if world == 1:
+            line["cpu_baseline"] = cpu_baseline_leg(a)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -102,6 +102,14 @@ class Batch:
         b.lam_in = self.lam_in.data_ptr() if self.lam_in is not None else None
         return b
 
+    def window(self, s0, s1):
+        """Sequences [s0, s1) of this batch as a Batch of views (no copy): the unit the wave loops launch on."""
+        return Batch(n_frames=self.n_frames[s0:s1], h=self.h[s0:s1], meas=self.meas[s0:s1], cams=self.cams[s0:s1],
+                     chain_vec=self.chain_vec[s0:s1], cam_model=self.cam_model,
+                     lam_eq=None if self.lam_eq is None else self.lam_eq[s0:s1],
+                     lam_in=None if self.lam_in is None else self.lam_in[s0:s1],
+                     mu_eq=self.mu_eq, mu_in=self.mu_in, loss=self.loss)
+
     @staticmethod
     def from_numpy(meas, cams, chain_vec, h, n_frames=None, device="cuda", cam_model=FISHEYE, meas_dtype=torch.float32):
         """meas[S,N,C,24,W,3|4] (u, v, gate), cams[S,C,24], chain_vec[S,24,5,3], h[S]."""
@@ -154,26 +162,28 @@ class Solver:
             self.v_in = torch.zeros(S, N, model.n_ineq, **f64)
 
     # ---- K1 --------------------------------------------------------------------------------------------------
-    def evaluate(self, q, pose=False, resid=False, constraints=False, jac=False, cost_out=None):
-        """cost[S,4] = (measurement, model, al_eq, al_in) and optional per-frame outputs."""
+    def evaluate(self, q, pose=False, resid=False, constraints=False, jac=False, cost_out=None, buffers=None):
+        """cost[S,4] = (measurement, model, al_eq, al_in) and optional per-frame outputs.  `buffers` may hold
+        preallocated output tensors ("pose", "resid", "jac") to write into instead of allocating."""
         b = self.b
         assert q.is_cuda and q.dtype == torch.float64 and q.is_contiguous() and q.shape == (b.S, b.N, 54)
         out = {}
+        buffers = buffers or {}
         eo = _lib.CpeEvalOut()
         eo.frame_cost = self.frame_cost.data_ptr()
         f64 = dict(dtype=torch.float64, device=q.device)
         if pose:
-            out["pose"] = torch.zeros(b.S, b.N, 24, 3, **f64)
+            out["pose"] = buffers["pose"] if "pose" in buffers else torch.zeros(b.S, b.N, 24, 3, **f64)
             eo.pose = out["pose"].data_ptr()
         if resid:
-            out["resid"] = torch.zeros(b.S, b.N, b.C, 24, b.W, 2, **f64)
+            out["resid"] = buffers["resid"] if "resid" in buffers else torch.zeros(b.S, b.N, b.C, 24, b.W, 2, **f64)
             eo.resid = out["resid"].data_ptr()
         if constraints:
             out["c_eq"] = self.c_eq if hasattr(self, "c_eq") else torch.zeros(b.S, b.N, 26, **f64)
             out["v_in"] = self.v_in if hasattr(self, "v_in") else torch.zeros(b.S, b.N, self.m.n_ineq, **f64)
             eo.c_eq, eo.v_in = out["c_eq"].data_ptr(), out["v_in"].data_ptr()
         if jac:
-            out["jac"] = torch.zeros(b.S, b.N, b.C, 24, b.W, 2, 18, **f64)
+            out["jac"] = buffers["jac"] if "jac" in buffers else torch.zeros(b.S, b.N, b.C, 24, b.W, 2, 18, **f64)
             eo.jac = out["jac"].data_ptr()
         bs = b.struct()
         st = _stream()
@@ -183,6 +193,25 @@ class Solver:
         self.launches += 2
         out["cost"] = cost
         return out
+
+    def evaluate_launch(self, q, buffers, cost_out, record_mid=None):
+        """Lean K1 launch for wave loops: residuals + chain-sparse Jacobian into preallocated `buffers`
+        ("resid", "jac"), then the per-sequence cost reduction into cost_out[S,4].  `record_mid` (a CUDA event)
+        is recorded between the two kernels so that the K1 launch can be timed on its own."""
+        eo = _lib.CpeEvalOut()
+        eo.frame_cost = self.frame_cost.data_ptr()
+        if "resid" in buffers:
+            eo.resid = buffers["resid"].data_ptr()
+        if "jac" in buffers:
+            eo.jac = buffers["jac"].data_ptr()
+        bs = self.b.struct()
+        st = _stream()
+        _lib.check(self.lib.cpe_eval_f64(C.byref(self.m.struct), C.byref(bs), _ptr(q), C.byref(eo), st), "cpe_eval_f64")
+        if record_mid is not None:
+            record_mid.record()
+        _lib.check(self.lib.cpe_reduce_cost_f64(C.byref(bs), _ptr(self.frame_cost), _ptr(cost_out), st),
+                   "cpe_reduce_cost_f64")
+        self.launches += 2
 
     # ---- K2 --------------------------------------------------------------------------------------------------
     def _asm_struct(self, raw=None, reduced=True):
@@ -275,3 +304,58 @@ class Solver:
         out = self.evaluate(q, constraints=True)
         return dict(q=q, cost=out["cost"].clone(), c_eq=out["c_eq"], v_in=out["v_in"], counters=self.counters.clone(),
                     status=self.status.clone(), lockstep_iterations=total_inner)
+
+
+class HostEvaluator:
+    """Residual + Jacobian evaluation for callers that keep their data in HOST memory (the reference-facing call:
+    what the L4 shim does once per LM iteration when q lives in numpy).  Sequences are streamed through the GPU
+    in waves of `wave` sequences on two streams with two staging sets, so the host->device copy of wave i+1
+    overlaps the kernel of wave i.  Per wave it calls `cpe_eval_host_f64` (include/cpe.h): H2D of q and the
+    detections, K1 with the chain-sparse Jacobian written to a device buffer, the per-sequence cost reduction,
+    and D2H of cost[S,4]."""
+
+    def __init__(self, model: Model, proto: Batch, S, wave, jac=True):
+        self.m, self.lib, self.proto = model, model.lib, proto
+        self.S, self.wave, self.N, self.C, self.W = S, wave, proto.N, proto.C, proto.W
+        dev = model.device
+        f64 = dict(dtype=torch.float64, device=dev)
+        self.streams = [torch.cuda.Stream(device=dev) for _ in range(2)]
+        self.stage = []
+        for _ in range(2):
+            st = dict(q=torch.empty(wave, self.N, 54, **f64),
+                      meas=torch.empty(wave, self.N, self.C, 24, self.W, 4, dtype=proto.meas.dtype, device=dev),
+                      frame_cost=torch.zeros(wave, self.N, 4, **f64), cost=torch.zeros(wave, 4, **f64),
+                      jac=torch.empty(wave, self.N, self.C, 24, self.W, 2, 18, **f64) if jac else None)
+            self.stage.append(st)
+        self.h_cost = torch.zeros(S, 4, dtype=torch.float64).pin_memory()
+        self.launches = 0
+
+    def bytes_per_call(self):
+        h2d = self.S * self.N * (54 * 8 + self.C * 24 * self.W * 4 * self.proto.meas.element_size())
+        return h2d, self.S * 4 * 8
+
+    def __call__(self, h_q, h_meas):
+        """h_q[S,N,54] f64 and h_meas[S,N,C,24,W,4] pinned host tensors -> pinned cost[S,4] (valid after return)."""
+        assert not h_q.is_cuda and not h_meas.is_cuda and h_q.is_pinned() and h_meas.is_pinned()
+        cur = torch.cuda.current_stream()
+        for st in self.streams:
+            st.wait_stream(cur)
+        for i, s0 in enumerate(range(0, self.S, self.wave)):
+            s1 = min(self.S, s0 + self.wave)
+            stg, stream = self.stage[i & 1], self.streams[i & 1]
+            bw = self.proto.window(s0, s1)
+            bs = bw.struct()
+            eo = _lib.CpeEvalOut()
+            eo.frame_cost = stg["frame_cost"].data_ptr()
+            if stg["jac"] is not None:
+                eo.jac = stg["jac"].data_ptr()
+            _lib.check(self.lib.cpe_eval_host_f64(
+                C.byref(self.m.struct), C.byref(bs), C.c_void_p(h_q[s0:s1].data_ptr()),
+                C.c_void_p(h_meas[s0:s1].data_ptr()), _ptr(stg["q"]), _ptr(stg["meas"]), C.byref(eo),
+                _ptr(stg["cost"]), C.c_void_p(self.h_cost[s0:s1].data_ptr()), None,
+                C.c_void_p(stream.cuda_stream)), "cpe_eval_host_f64")
+            self.launches += 2
+        for st in self.streams:
+            cur.wait_stream(st)
+        cur.synchronize()
+        return self.h_cost

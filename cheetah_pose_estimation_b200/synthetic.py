@@ -202,3 +202,65 @@ def make_problem(S=1, N=100, C=6, seed=0, fps=120.0, animal="jules", projector=N
     q_init[:, :, 5::3] = head[:, None, None]
     return SyntheticProblem(q_true=q_true, q_init=q_init, cams=cams, chain_link=chain_link, chain_vec=chain_vec,
                             h=np.full(S, 1.0 / fps), meas=meas, n_frames=np.full(S, N, np.int32), fps=fps)
+
+
+def make_device_problem(S, N=500, C=6, seed=0, fps=120.0, animal="jules", device="cuda", n_unique=32, chunk=256,
+                        outlier_frac=0.10, image_size=(1920, 1080)):
+    """The large sweep built directly in HBM: `n_unique` distinct trajectories / camera rings are
+    generated on the host exactly as in make_problem, projected once by the CUDA kernel, tiled to S sequences, and
+    the per-sequence detection noise, likelihoods and outliers are drawn on the device (torch generator).
+    Returns (Batch, q_true[S,N,54], q_init[S,N,54]) as device tensors."""
+    import torch
+    from . import engine
+    dev = torch.device(device)
+    rng = np.random.default_rng(seed)
+    nu = min(S, n_unique)
+    lengths, radii, _ = sk.animal(animal)
+    _, cvec = sk.marker_chains(lengths, radii)
+    q_u = make_trajectories(nu, N, fps, rng)
+    cams_u = make_cameras(nu, C, rng)
+    cvec_u = np.tile(cvec[None], (nu, 1, 1, 1))
+    uv_u = torch.as_tensor(cuda_projector(device)(q_u, cams_u, cvec_u), device=dev)           # [nu,N,C,24,2]
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(int(seed) + 12345)
+    sigma = torch.as_tensor(1.0 / sk.measurement_weights()[0] / 2.0, device=dev)               # [24]
+    meas = torch.empty(S, N, C, 24, 1, 4, dtype=torch.float32, device=dev)
+    idx_all = torch.arange(S, device=dev) % nu
+    W_, H_ = image_size
+    for s0 in range(0, S, chunk):
+        s1 = min(S, s0 + chunk)
+        uv = uv_u[idx_all[s0:s1]]
+        shp = uv.shape[:-1]
+        det = uv + torch.randn(uv.shape, generator=gen, device=dev, dtype=torch.float64) * sigma[None, None, None, :, None]
+        # likelihood ~ Beta(8,2) as the ratio of two gamma draws
+        ga = torch._standard_gamma(torch.full(shp, 8.0, device=dev, dtype=torch.float32), generator=gen)
+        gb = torch._standard_gamma(torch.full(shp, 2.0, device=dev, dtype=torch.float32), generator=gen)
+        lik = ga / (ga + gb)
+        out = torch.rand(shp, generator=gen, device=dev) < outlier_frac
+        ou = torch.rand(shp, generator=gen, device=dev, dtype=torch.float64) * W_
+        ov = torch.rand(shp, generator=gen, device=dev, dtype=torch.float64) * H_
+        det = torch.where(out[..., None], torch.stack([ou, ov], -1), det)
+        low = out & (torch.rand(shp, generator=gen, device=dev) < 0.5)
+        lik = torch.where(low, torch.rand(shp, generator=gen, device=dev) * 0.5, lik)
+        outside = (uv[..., 0] < 0) | (uv[..., 0] >= W_) | (uv[..., 1] < 0) | (uv[..., 1] >= H_)
+        outside |= ~torch.isfinite(uv).all(-1)
+        lik = torch.where(outside, torch.zeros_like(lik), lik)
+        det = torch.where(outside[..., None], torch.zeros_like(det), det)
+        m = meas[s0:s1, :, :, :, 0]
+        m[..., 0:2] = det.to(torch.float32)
+        m[..., 2] = (lik > 0.5).to(torch.float32)
+        m[..., 3] = 0.0
+    q_true_u = torch.as_tensor(q_u, device=dev)
+    q_true = q_true_u[idx_all].contiguous()
+    q_init = torch.zeros_like(q_true)
+    q_init[:, :, 0:3] = q_true[:, :, 0:3] + 0.03 * torch.randn(S, N, 3, generator=gen, device=dev, dtype=torch.float64)
+    head = np.pi + np.arctan2(q_u[:, -1, 1] - q_u[:, 0, 1], q_u[:, -1, 0] - q_u[:, 0, 0])
+    head = head + 2 * np.pi * np.round((q_u[:, 0, 5] - head) / (2 * np.pi))
+    q_init[:, :, 5::3] = torch.as_tensor(head, device=dev)[idx_all][:, None, None]
+    batch = engine.Batch(
+        n_frames=torch.full((S,), N, dtype=torch.int32, device=dev),
+        h=torch.full((S,), 1.0 / fps, dtype=torch.float64, device=dev),
+        meas=meas,
+        cams=torch.as_tensor(cams_u, device=dev)[idx_all].contiguous(),
+        chain_vec=torch.as_tensor(cvec, device=dev)[None].expand(S, -1, -1, -1).contiguous())
+    return batch, q_true, q_init
