@@ -212,7 +212,7 @@ def run_b200(a):
     gen.manual_seed(a.seed + 100 + rank)
     q = (q_true + 0.05 * torch.randn(q_true.shape, generator=gen, device=dev, dtype=torch.float64)).contiguous()
     f64 = dict(dtype=torch.float64, device=dev)
-    bufs = {"jac": torch.empty(wave, N, C, 24, 1, 2, 18, **f64), "resid": torch.empty(wave, N, C, 24, 1, 2, **f64)}
+    bufs = {"jac": torch.empty(wave, N, C, model.jac_width, **f64), "resid": torch.empty(wave, N, C, 24, 1, 2, **f64)}
     waves = []
     for s0 in range(0, S, wave):
         s1 = min(S, s0 + wave)
@@ -368,7 +368,7 @@ def main():
         achieved = fv_launch * ALGO_BYTES_PER_FV / (kern_ms * 1e-3) / 1e9
         traffic = None
         try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("frame_kernel_eval_jac")
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("eval_kernel_jac")
         except (OSError, ValueError):
             pass
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
@@ -378,7 +378,7 @@ def main():
                            "l2": "inputs+outputs per launch (>= 20 GB) exceed the 126 MB L2; no flush needed",
                            "sharding": f"sequences, {a.seqs}/rank, no data-path collective"},
                 "gpu_launches": int(stats[4].item()),
-                "kernel": {"name": "frame_kernel<MODE_EVAL_JAC>", "avg_ms": kern_ms, "frame_views_per_launch": fv_launch},
+                "kernel": {"name": "eval_kernel<JAC>", "avg_ms": kern_ms, "frame_views_per_launch": fv_launch},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                              "frac": achieved / peak, "traffic": traffic,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650",

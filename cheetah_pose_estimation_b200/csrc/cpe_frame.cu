@@ -550,13 +550,6 @@ static int launch_frame(const cpe_model *model, const cpe_batch *b, const double
 
 }  // namespace cpe
 
-extern "C" int cpe_eval_f64(const cpe_model *model, const cpe_batch *batch, const double *q, const cpe_eval_out *out,
-                            void *stream) {
-    if (!out) return CPE_E_NULL;
-    if (out->jac) return cpe::launch_frame<cpe::MODE_EVAL_JAC>(model, batch, q, nullptr, out, nullptr, (cudaStream_t)stream);
-    return cpe::launch_frame<cpe::MODE_EVAL>(model, batch, q, nullptr, out, nullptr, (cudaStream_t)stream);
-}
-
 extern "C" int cpe_assemble_f64(const cpe_model *model, const cpe_batch *batch, const double *q, const double *damp,
                                 const cpe_assemble_out *out, void *stream) {
     if (!out) return CPE_E_NULL;

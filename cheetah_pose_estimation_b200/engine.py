@@ -15,7 +15,7 @@ from . import _lib, skeleton
 FISHEYE, PINHOLE = 0, 1
 _I32_KEYS = ("chain_link", "slot_of", "eq_pairs", "ineq_idx", "ind_idx", "ind_pos", "blk_nodes", "blk_id",
              "blk_item_ptr", "blk_items", "blk_eq_ptr", "blk_eq_items", "grp_ndep", "grp_nnb", "grp_dep", "grp_nb",
-             "grp_nbpos")
+             "grp_nbpos", "u_off", "u_item")
 _F64_KEYS = ("ineq_bounds", "wq", "meas_w")
 
 
@@ -47,6 +47,8 @@ class Model:
         s = _lib.CpeModel()
         s.n_ineq, s.n_blocks = self.n_ineq, int(self.tables["n_blocks"])
         s.n_groups, s.n_blk_items = self.n_groups, int(self.tables["n_blk_items"])
+        s.n_u = int(self.tables["n_u"])
+        self.jac_width = 2 * (72 + s.n_u)
         for k in _I32_KEYS + _F64_KEYS:
             setattr(s, k, self.t[k].data_ptr())
         self.struct = s
@@ -183,7 +185,7 @@ class Solver:
             out["v_in"] = self.v_in if hasattr(self, "v_in") else torch.zeros(b.S, b.N, self.m.n_ineq, **f64)
             eo.c_eq, eo.v_in = out["c_eq"].data_ptr(), out["v_in"].data_ptr()
         if jac:
-            out["jac"] = buffers["jac"] if "jac" in buffers else torch.zeros(b.S, b.N, b.C, 24, b.W, 2, 18, **f64)
+            out["jac"] = buffers["jac"] if "jac" in buffers else torch.zeros(b.S, b.N, b.C, self.m.jac_width, **f64)
             eo.jac = out["jac"].data_ptr()
         bs = b.struct()
         st = _stream()
@@ -325,7 +327,7 @@ class HostEvaluator:
             st = dict(q=torch.empty(wave, self.N, 54, **f64),
                       meas=torch.empty(wave, self.N, self.C, 24, self.W, 4, dtype=proto.meas.dtype, device=dev),
                       frame_cost=torch.zeros(wave, self.N, 4, **f64), cost=torch.zeros(wave, 4, **f64),
-                      jac=torch.empty(wave, self.N, self.C, 24, self.W, 2, 18, **f64) if jac else None)
+                      jac=torch.empty(wave, self.N, self.C, model.jac_width, **f64) if jac else None)
             self.stage.append(st)
         self.h_cost = torch.zeros(S, 4, dtype=torch.float64).pin_memory()
         self.launches = 0

@@ -201,6 +201,43 @@ def relative_matrix():
     return T
 
 
+def jacobian_pattern(chain_link=None):
+    """Static pattern of the packed chain-sparse Jacobian (include/cpe.h, `cpe_eval_out.jac`).
+
+    Returns (u_off[25], u_item[n_u], cols) where cols[l] lists the coordinate indices (into q[54]) of marker l's
+    columns: base x,y,z then (phi,theta,psi) of every chain link.  Marker l owns 2*len(cols[l]) consecutive entries
+    of the 540-vector of one frame.view, starting at 2*(3*l + u_off[l]): the u row, then the v row."""
+    if chain_link is None:
+        lengths, radii, _ = animal("jules")
+        chain_link, _ = marker_chains(lengths, radii)
+    u_off, u_item, cols = [0], [], []
+    for l in range(N_MARKERS):
+        cl = [0, 1, 2]
+        for j in range(MAX_CHAIN):
+            li = int(chain_link[l, j])
+            if li < 0:
+                break
+            for a in range(3):
+                u_item.append((l << 8) | (j << 4) | a)
+                cl.append(3 + 3 * li + a)
+        u_off.append(len(u_item))
+        cols.append(cl)
+    return np.array(u_off, np.int32), np.array(u_item, np.int32), cols
+
+
+def jacobian_to_dense(jac_packed, chain_link=None):
+    """Packed [..., 540] -> dense [..., 24, 2, 54] (host-side helper for consumers and tests)."""
+    u_off, _, cols = jacobian_pattern(chain_link)
+    jac_packed = np.asarray(jac_packed)
+    out = np.zeros(jac_packed.shape[:-1] + (N_MARKERS, 2, N_COORDS), jac_packed.dtype)
+    for l in range(N_MARKERS):
+        n = len(cols[l])
+        o = 2 * (3 * l + int(u_off[l]))
+        out[..., l, 0, cols[l]] = jac_packed[..., o:o + n]
+        out[..., l, 1, cols[l]] = jac_packed[..., o + n:o + 2 * n]
+    return out
+
+
 def build_tables(kinetic_dataset=False):
     """All static integer/float tables of `cpe_model` (include/cpe.h) as a dict of numpy arrays."""
     lengths, radii, _ = animal("jules")                      # topology only
@@ -279,7 +316,9 @@ def build_tables(kinetic_dataset=False):
         grp_nb[g, :len(nbs)] = nbs
         for j, p in enumerate(nbs):
             grp_nbpos[g, ind_pos[p]] = j
+    u_off, u_item, jac_cols = jacobian_pattern(chain_link)
     return dict(
+        u_off=u_off, u_item=u_item, n_u=len(u_item),
         chain_link=chain_link.reshape(-1), slot_of=slot_of.reshape(-1), eq_pairs=eq.reshape(-1),
         ineq_idx=ineq_idx.reshape(-1), ineq_bounds=ineq_bounds.reshape(-1), wq=motion_weights(),
         meas_w=measurement_weights(kinetic_dataset).reshape(-1), ind_idx=ind, ind_pos=ind_pos,

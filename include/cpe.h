@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 100          /* 0.1.0 */
+#define CPE_VERSION 101          /* 0.1.1 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -65,6 +65,8 @@ typedef struct cpe_model {
     int32_t n_blocks;               /* nonzero lower-triangular 3x3 node-pair blocks of the frame Hessian */
     int32_t n_groups;               /* elimination groups of dependent coordinates */
     int32_t n_blk_items;
+    int32_t n_u;                    /* packed chain columns over all markers: sum_l 3*chainlen(l) (198) */
+    int32_t reserved_;
     const int32_t *chain_link;      /* [24*5] link index or -1 */
     const int32_t *slot_of;         /* [24*18] slot (0 = xyz, 1..5 = chain position) of node in marker chain, or -1 */
     const int32_t *eq_pairs;        /* [26*4] link_a, link_b, axis_a, axis_b : (R_a e_axa).(R_b e_axb) = 0 */
@@ -85,6 +87,8 @@ typedef struct cpe_model {
     const int32_t *grp_dep;         /* [n_groups*6] coordinate indices */
     const int32_t *grp_nb;          /* [n_groups*12] coordinate indices (independent) */
     const int32_t *grp_nbpos;       /* [n_groups*28] position of ind coord r in the group's nb list, or -1 */
+    const int32_t *u_off;           /* [25] first packed chain column of marker l (prefix sum of 3*chainlen) */
+    const int32_t *u_item;          /* [n_u] (marker << 8) | (chain slot << 4) | angle, per packed chain column */
 } cpe_model;
 
 /* One batch of sequences. */
@@ -110,7 +114,10 @@ typedef struct cpe_eval_out {
     double *resid;                  /* [S,N,C,24,W,2] slack = proj - meas (what the reference saves as meas_err) */
     double *c_eq;                   /* [S,N,26] */
     double *v_in;                   /* [S,N,n_ineq]  t - clamp(t, lo, up), t = d + lam/mu */
-    double *jac;                    /* [S,N,C,24,W,2,18] d(u,v)/d(chain coords: xyz, then 5 x 3 link angles) */
+    double *jac;                    /* [S,N,C,2*(72+n_u)] packed chain-sparse d(u,v)/dq (540 per frame.view): marker l owns
+                                       2*ncol(l) entries at 2*(3l+u_off[l]), ncol = 3 + u_off[l+1]-u_off[l]: first the
+                                       u row then the v row, columns = base x,y,z then (phi,theta,psi) of each chain
+                                       link in chain order.  Independent of the hypothesis index w. */
 } cpe_eval_out;
 
 /* Outputs of cpe_assemble: the per-frame reduced normal equations after Marquardt damping and elimination. */
