@@ -18,7 +18,9 @@
 // with coalesced float4 loads issued before the FK phase.  No atomics: every reduction has a fixed order, so a
 // sequence's results are bit-identical whatever its batch neighbours are.
 #include <cuda_runtime.h>
+#include <math.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "cpe.h"
 #include "cpe_internal.cuh"
@@ -36,11 +38,12 @@ struct EvalParams {
     int n_u;        // packed chain columns per marker set (198 for the cheetah)
     int fs;         // per-frame shared stride (doubles)
     int off_stage;  // offset (doubles) of the Jacobian staging tile
+    double ea, eb, ec;  // exp(loss_a), exp(loss_b), exp(loss_c)
 };
 
 // per-frame shared layout (doubles)
 constexpr int QO = 0, SCO = 56, RO = 160, POSO = 314, UO = 386;
-__host__ __device__ inline int contrib_off(int n_u) { return UO + ((3 * n_u + 1) & ~1); }
+__host__ __device__ inline int contrib_off(int n_u) { return UO + 10 * (n_u / 3); }   // U: 10 doubles per (marker, link)
 // contributions: eq[26] in[32] mo[54] me[TPF]
 constexpr int EQC = 0, INC = 26, MOC = 58, MEC = 112;
 
@@ -91,174 +94,179 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
-template <bool JAC>
-__global__ void __launch_bounds__(288, 2) eval_kernel(const __grid_constant__ EvalParams p) {
+template <bool JAC, int MAXT, int MINB>
+__global__ void __launch_bounds__(MAXT, MINB) eval_kernel(const __grid_constant__ EvalParams p) {
     extern __shared__ __align__(16) double sm[];
-    const int tid = threadIdx.x, nt = blockDim.x;
+    const int tid = threadIdx.x;
     const int N = p.b.N, C = p.b.C, W = p.b.W, F = p.F, TPF = p.TPF;
     const int s = blockIdx.x / p.chunks;
     const int k0 = (blockIdx.x - s * p.chunks) * F;
     const int nf = p.b.n_frames[s];
     if (k0 >= nf) return;
     const int nv = min(F, nf - k0);                       // valid frames of this CTA
-    const int n_ineq = p.m.n_ineq, n_u = p.n_u;
+    const int n_ineq = p.m.n_ineq, n_u = p.n_u, n_ul = n_u / 3;
     const int FS = p.fs, CO = contrib_off(n_u);
     double *cam = sm;                                      // [C*24]
-    double *frames = sm + C * CPE_CAM_STRIDE;              // [F][FS]
     double *stage = sm + p.off_stage;                      // [F][C][540]
     const size_t f0 = (size_t)s * N + k0;                 // global index of the first frame
 
-    // ---- main-phase role of this thread; issue its detection load early ---------------------------------------
-    const int mf = tid / TPF, mtask = tid - mf * TPF;
+    // Every thread belongs to ONE frame of the CTA for all phases: frame mf, local index mt in [0, TPF).
+    const int mf = tid / TPF, mt = tid - mf * TPF;
     const bool mvalid = mf < nv;
-    const int mc = mtask / 24, ml = mtask - mc * 24;
-    const size_t midx0 = (((f0 + mf) * C + mc) * 24 + ml) * W;
+    double *fr = sm + C * CPE_CAM_STRIDE + mf * FS;
+    const size_t fidx = f0 + mf;
+    const int mc = mt / 24, ml = mt - mc * 24;
+    const size_t midx0 = ((fidx * C + mc) * 24 + ml) * W;
+    // issue the detection load before the FK phases
     float4 m4 = make_float4(0.f, 0.f, 0.f, 0.f);
     double4 m8 = make_double4(0.0, 0.0, 0.0, 0.0);
+    const bool m64 = p.b.meas_is_f64 != 0;
     if (mvalid) {
-        if (p.b.meas_is_f64) m8 = reinterpret_cast<const double4 *>(p.b.meas)[midx0];
+        if (m64) m8 = reinterpret_cast<const double4 *>(p.b.meas)[midx0];
         else m4 = __ldg(reinterpret_cast<const float4 *>(p.b.meas) + midx0);
     }
-
-    for (int i = tid; i < nv * 54; i += nt) {
-        const int f = i / 54, c = i - f * 54;
-        frames[f * FS + QO + c] = p.q[(f0 + f) * 54 + c];
+    const double *qf = p.q + fidx * 54;
+    if (mvalid) {
+        for (int c = mt; c < 54; c += TPF) fr[QO + c] = qf[c];
     }
-    for (int i = tid; i < C * CPE_CAM_STRIDE; i += nt) cam[i] = p.b.cams[(size_t)s * C * CPE_CAM_STRIDE + i];
+    for (int i = tid; i < C * CPE_CAM_STRIDE; i += blockDim.x) cam[i] = p.b.cams[(size_t)s * C * CPE_CAM_STRIDE + i];
     __syncthreads();
-    for (int i = tid; i < nv * 51; i += nt) {
-        const int f = i / 51, a = i - f * 51;
-        double *fr = frames + f * FS;
-        sincos(fr[QO + 3 + a], &fr[SCO + 2 * a], &fr[SCO + 2 * a + 1]);
+    if (mvalid) {
+        for (int a = mt; a < 51; a += TPF) sincos(fr[QO + 3 + a], &fr[SCO + 2 * a], &fr[SCO + 2 * a + 1]);
     }
     __syncthreads();
-    for (int i = tid; i < nv * 17; i += nt) {
-        const int f = i / 17, link = i - f * 17;
-        double *fr = frames + f * FS;
-        rot_from_sc(fr + SCO + 6 * link, fr + RO + 9 * link);
+    if (mvalid) {
+        for (int link = mt; link < 17; link += TPF) rot_from_sc(fr + SCO + 6 * link, fr + RO + 9 * link);
     }
     __syncthreads();
 
     // ---- camera-independent per-frame items -------------------------------------------------------------------
-    const double *cvec = p.b.chain_vec + (size_t)s * 24 * CPE_MAX_CHAIN * 3;
-    const double h = p.b.h[s];
-    const double mu_eq = p.b.mu_eq, mu_in = p.b.mu_in;
-    const int n_items = 24 + (JAC ? n_u : 0) + 26 + n_ineq + 54;
-    for (int i = tid; i < nv * n_items; i += nt) {
-        const int f = i / n_items;
-        int it = i - f * n_items;
-        double *fr = frames + f * FS;
-        const size_t fidx = f0 + f;
-        if (it < 24) {
-            const int l = it;
-            double x = fr[QO + 0], y = fr[QO + 1], z = fr[QO + 2];
+    if (mvalid) {
+        const double *cvec = p.b.chain_vec + (size_t)s * 24 * CPE_MAX_CHAIN * 3;
+        const int32_t *chain_link = p.m.chain_link;
+        const int n_uit = JAC ? n_u : 0;
+        const int n_items = 24 + n_uit + 26 + n_ineq + 54;
+        double *ctr = fr + CO;
+        for (int it0 = mt; it0 < n_items; it0 += TPF) {
+            int it = it0;
+            if (it < 24) {
+                const int l = it;
+                double x = fr[QO + 0], y = fr[QO + 1], z = fr[QO + 2];
 #pragma unroll
-            for (int j = 0; j < CPE_MAX_CHAIN; ++j) {
-                const int link = p.m.chain_link[l * CPE_MAX_CHAIN + j];
-                if (link < 0) break;
-                const double *Rl = fr + RO + link * 9;
-                const double *v = cvec + (l * CPE_MAX_CHAIN + j) * 3;
-                const double v0 = v[0], v1 = v[1], v2 = v[2];
-                x += Rl[0] * v0 + Rl[1] * v1 + Rl[2] * v2;
-                y += Rl[3] * v0 + Rl[4] * v1 + Rl[5] * v2;
-                z += Rl[6] * v0 + Rl[7] * v1 + Rl[8] * v2;
-            }
-            fr[POSO + l * 3 + 0] = x; fr[POSO + l * 3 + 1] = y; fr[POSO + l * 3 + 2] = z;
-            if (p.eo.pose) {
-                double *o = p.eo.pose + (fidx * 24 + l) * 3;
-                o[0] = x; o[1] = y; o[2] = z;
-            }
-            continue;
-        }
-        it -= 24;
-        if (JAC) {
-            if (it < n_u) {
-                const int code = p.m.u_item[it];
-                const int l = code >> 8, j = (code >> 4) & 15, a = code & 15;
-                const int link = p.m.chain_link[l * CPE_MAX_CHAIN + j];
-                const double *v = cvec + (l * CPE_MAX_CHAIN + j) * 3;
-                drot_times(fr + SCO + 6 * link, a, v[0], v[1], v[2], fr + UO + 3 * it);
+                for (int j = 0; j < CPE_MAX_CHAIN; ++j) {
+                    const int link = chain_link[l * CPE_MAX_CHAIN + j];
+                    if (link >= 0) {
+                        const double *Rl = fr + RO + link * 9;
+                        const double *v = cvec + (l * CPE_MAX_CHAIN + j) * 3;
+                        const double v0 = v[0], v1 = v[1], v2 = v[2];
+                        x += Rl[0] * v0 + Rl[1] * v1 + Rl[2] * v2;
+                        y += Rl[3] * v0 + Rl[4] * v1 + Rl[5] * v2;
+                        z += Rl[6] * v0 + Rl[7] * v1 + Rl[8] * v2;
+                    }
+                }
+                fr[POSO + l * 3 + 0] = x; fr[POSO + l * 3 + 1] = y; fr[POSO + l * 3 + 2] = z;
+                if (p.eo.pose) {
+                    double *o = p.eo.pose + (fidx * 24 + l) * 3;
+                    o[0] = x; o[1] = y; o[2] = z;
+                }
                 continue;
             }
-            it -= n_u;
-        }
-        double *ctr = fr + CO;
-        if (it < 26) {
-            const int e = it;
-            const int la = p.m.eq_pairs[e * 4 + 0], lb = p.m.eq_pairs[e * 4 + 1];
-            const int ia = p.m.eq_pairs[e * 4 + 2], ib = p.m.eq_pairs[e * 4 + 3];
-            const double *Ra = fr + RO + la * 9, *Rb = fr + RO + lb * 9;
-            const double c = Ra[ia] * Rb[ib] + Ra[3 + ia] * Rb[3 + ib] + Ra[6 + ia] * Rb[6 + ib];
-            const double lam = p.b.lam_eq ? p.b.lam_eq[fidx * 26 + e] : 0.0;
-            const double t = c + lam / mu_eq;
-            ctr[EQC + e] = 0.5 * mu_eq * t * t;
-            if (p.eo.c_eq) p.eo.c_eq[fidx * 26 + e] = c;
-            continue;
-        }
-        it -= 26;
-        if (it < n_ineq) {
-            const int j = it;
-            const int ip = p.m.ineq_idx[2 * j], im = p.m.ineq_idx[2 * j + 1];
-            const double lo = p.m.ineq_bounds[2 * j], up = p.m.ineq_bounds[2 * j + 1];
-            const double d = fr[QO + ip] - (im >= 0 ? fr[QO + im] : 0.0);
-            const double lam = p.b.lam_in ? p.b.lam_in[fidx * n_ineq + j] : 0.0;
-            const double t = d + lam / mu_in;
-            const double v = t - fmin(fmax(t, lo), up);
-            ctr[INC + j] = 0.5 * mu_in * v * v;
-            if (p.eo.v_in) p.eo.v_in[fidx * n_ineq + j] = v;
-            continue;
-        }
-        it -= n_ineq;
-        {
-            const int c = it;
-            const double w = p.m.wq[c];
-            double val = 0.0;
-            if (w != 0.0 && k0 + f >= 3) {
-                const double *qf = p.q + fidx * 54;
-                const double d3 = (fr[QO + c] - 3.0 * qf[c - 54] + 3.0 * qf[c - 108] - qf[c - 162]) / (h * h);
-                val = w * d3 * d3;
+            it -= 24;
+            if (JAC) {
+                if (it < n_uit) {
+                    const int code = p.m.u_item[it];
+                    const int l = code >> 8, j = (code >> 4) & 15, a = code & 15;
+                    const int link = chain_link[l * CPE_MAX_CHAIN + j];
+                    const double *v = cvec + (l * CPE_MAX_CHAIN + j) * 3;
+                    // U block of one (marker, chain link): 3 angles x 3 components, padded to 10 doubles
+                    drot_times(fr + SCO + 6 * link, a, v[0], v[1], v[2], fr + UO + 10 * (it / 3) + 3 * a);
+                    continue;
+                }
+                it -= n_uit;
             }
-            ctr[MOC + c] = val;
+            if (it < 26) {
+                const int e = it;
+                const int4 pr4 = reinterpret_cast<const int4 *>(p.m.eq_pairs)[e];
+                const double *Ra = fr + RO + pr4.x * 9, *Rb = fr + RO + pr4.y * 9;
+                const int ia = pr4.z, ib = pr4.w;
+                const double c = Ra[ia] * Rb[ib] + Ra[3 + ia] * Rb[3 + ib] + Ra[6 + ia] * Rb[6 + ib];
+                const double lam = p.b.lam_eq ? p.b.lam_eq[fidx * 26 + e] : 0.0;
+                const double t = c + lam / p.b.mu_eq;
+                ctr[EQC + e] = 0.5 * p.b.mu_eq * t * t;
+                if (p.eo.c_eq) p.eo.c_eq[fidx * 26 + e] = c;
+                continue;
+            }
+            it -= 26;
+            if (it < n_ineq) {
+                const int j = it;
+                const int ip = p.m.ineq_idx[2 * j], im = p.m.ineq_idx[2 * j + 1];
+                const double lo = p.m.ineq_bounds[2 * j], up = p.m.ineq_bounds[2 * j + 1];
+                const double d = fr[QO + ip] - (im >= 0 ? fr[QO + im] : 0.0);
+                const double lam = p.b.lam_in ? p.b.lam_in[fidx * n_ineq + j] : 0.0;
+                const double t = d + lam / p.b.mu_in;
+                const double v = t - fmin(fmax(t, lo), up);
+                ctr[INC + j] = 0.5 * p.b.mu_in * v * v;
+                if (p.eo.v_in) p.eo.v_in[fidx * n_ineq + j] = v;
+                continue;
+            }
+            it -= n_ineq;
+            {
+                const int c = it;
+                const double w = p.m.wq[c];
+                double val = 0.0;
+                if (w != 0.0 && k0 + mf >= 3) {
+                    const double h = p.b.h[s];
+                    const double d3 = (fr[QO + c] - 3.0 * qf[c - 54] + 3.0 * qf[c - 108] - qf[c - 162]) / (h * h);
+                    val = w * d3 * d3;
+                }
+                ctr[MOC + c] = val;
+            }
         }
     }
     __syncthreads();
 
-    // ---- one thread per (frame, camera, marker): projection, residuals, robust loss, Jacobian rows ----------------
+    // ---- one thread per (frame, camera, marker): projection, residuals, robust loss, Jacobian columns -------------
     if (mvalid) {
-        double *fr = frames + mf * FS;
         const double la_ = p.b.loss_a, lb_ = p.b.loss_b, lc_ = p.b.loss_c;
-        const double ea = exp(la_), eb = exp(lb_), ec = exp(lc_);
+        const double ea = p.ea, eb = p.eb, ec = p.ec;
         const double *cm = cam + mc * CPE_CAM_STRIDE;
         Proj pr;
         project_point<JAC>(fr + POSO + ml * 3, cm, p.b.cam_model, pr);
         double rho = 0.0;
+        const double cmult = cm[20];
         for (int w = 0; w < W; ++w) {
             double um, vm, gate;
             if (w > 0) {
-                if (p.b.meas_is_f64) m8 = reinterpret_cast<const double4 *>(p.b.meas)[midx0 + w];
+                if (m64) m8 = reinterpret_cast<const double4 *>(p.b.meas)[midx0 + w];
                 else m4 = __ldg(reinterpret_cast<const float4 *>(p.b.meas) + midx0 + w);
             }
-            if (p.b.meas_is_f64) { um = m8.x; vm = m8.y; gate = m8.z; }
+            if (m64) { um = m8.x; vm = m8.y; gate = m8.z; }
             else { um = (double)m4.x; vm = (double)m4.y; gate = (double)m4.z; }
-            const double wgt = gate * p.m.meas_w[w * 24 + ml] * cm[20];
+            const double wgt = gate * p.m.meas_w[w * 24 + ml] * cmult;
             const double ru = pr.u - um, rv = pr.v - vm;
             if (p.eo.resid) reinterpret_cast<double2 *>(p.eo.resid)[midx0 + w] = make_double2(ru, rv);
             rho += redescending_value(fabs(wgt * ru), la_, lb_, lc_, ea, eb, ec);
             rho += redescending_value(fabs(wgt * rv), la_, lb_, lc_, ea, eb, ec);
         }
-        fr[CO + MEC + mtask] = rho;
+        fr[CO + MEC + mt] = rho;
         if (JAC) {
-            const int uo0 = p.m.u_off[ml], ncu = p.m.u_off[ml + 1] - uo0;      // chain columns of this marker
-            const int ncol = 3 + ncu;
-            double *ju = stage + ((size_t)mf * C + mc) * (2 * (72 + n_u)) + 2 * (3 * ml + uo0);
-            double *jv = ju + ncol;
-            ju[0] = pr.du[0]; ju[1] = pr.du[1]; ju[2] = pr.du[2];
-            jv[0] = pr.dv[0]; jv[1] = pr.dv[1]; jv[2] = pr.dv[2];
-            const double *U = fr + UO + 3 * uo0;
-            for (int j = 0; j < ncu; ++j) {
-                const double u0 = U[3 * j], u1 = U[3 * j + 1], u2 = U[3 * j + 2];
-                ju[3 + j] = pr.du[0] * u0 + pr.du[1] * u1 + pr.du[2] * u2;
-                jv[3 + j] = pr.dv[0] * u0 + pr.dv[1] * u1 + pr.dv[2] * u2;
+            const int uo0 = p.m.u_off[ml], nlk = (p.m.u_off[ml + 1] - uo0) / 3;      // chain links of this marker
+            // marker block of the packed Jacobian: (3 + 3 nlk) columns, each a (du, dv) pair
+            double2 *jc = reinterpret_cast<double2 *>(stage + ((size_t)mf * C + mc) * (2 * (72 + n_u)) + 2 * (3 * ml + uo0));
+            jc[0] = make_double2(pr.du[0], pr.dv[0]);
+            jc[1] = make_double2(pr.du[1], pr.dv[1]);
+            jc[2] = make_double2(pr.du[2], pr.dv[2]);
+            const double2 *U2 = reinterpret_cast<const double2 *>(fr + UO + 10 * (uo0 / 3));
+            for (int j = 0; j < nlk; ++j) {
+                const double2 a0 = U2[5 * j], a1 = U2[5 * j + 1], a2 = U2[5 * j + 2], a3 = U2[5 * j + 3],
+                              a4 = U2[5 * j + 4];
+                double2 *o = jc + 3 + 3 * j;
+                o[0] = make_double2(pr.du[0] * a0.x + pr.du[1] * a0.y + pr.du[2] * a1.x,
+                                    pr.dv[0] * a0.x + pr.dv[1] * a0.y + pr.dv[2] * a1.x);
+                o[1] = make_double2(pr.du[0] * a1.y + pr.du[1] * a2.x + pr.du[2] * a2.y,
+                                    pr.dv[0] * a1.y + pr.dv[1] * a2.x + pr.dv[2] * a2.y);
+                o[2] = make_double2(pr.du[0] * a3.x + pr.du[1] * a3.y + pr.du[2] * a4.x,
+                                    pr.dv[0] * a3.x + pr.dv[1] * a3.y + pr.dv[2] * a4.x);
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         }
@@ -275,9 +283,9 @@ __global__ void __launch_bounds__(288, 2) eval_kernel(const __grid_constant__ Ev
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
     }
     if (p.eo.frame_cost) {
-        const int wid = tid >> 5, lane = tid & 31, nw = nt >> 5;
+        const int wid = tid >> 5, lane = tid & 31, nw = blockDim.x >> 5;
         for (int f = wid; f < nv; f += nw) {
-            const double *ctr = frames + f * FS + CO;
+            const double *ctr = sm + C * CPE_CAM_STRIDE + f * FS + CO;
             double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
             for (int i = lane; i < TPF; i += 32) a0 += ctr[MEC + i];
             for (int i = lane; i < 54; i += 32) a1 += ctr[MOC + i];
@@ -291,6 +299,25 @@ __global__ void __launch_bounds__(288, 2) eval_kernel(const __grid_constant__ Ev
         }
     }
     if (JAC && tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    (void)n_ul;
+}
+
+template <bool JAC, int MAXT, int MINB>
+static int launch_cfg(const EvalParams &p, int grid, int threads, size_t smem, cudaStream_t st) {
+    cudaError_t e = cudaFuncSetAttribute(eval_kernel<JAC, MAXT, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    eval_kernel<JAC, MAXT, MINB><<<grid, threads, smem, st>>>(p);
+    return (int)cudaGetLastError();
+}
+
+static int eval_cfg() {
+    static int cfg = -1;
+    if (cfg < 0) {
+        const char *e = getenv("CPE_EVAL_CFG");      // tuning knob for experiments; default chosen by measurement
+        cfg = e ? atoi(e) : 3;
+    }
+    return cfg;
 }
 
 static int launch_eval(const cpe_model *model, const cpe_batch *b, const double *q, const cpe_eval_out *eo,
@@ -300,10 +327,13 @@ static int launch_eval(const cpe_model *model, const cpe_batch *b, const double 
     if (model->n_ineq > CPE_MAX_INEQ || model->n_u <= 0 || model->n_u > 240) return CPE_E_DIM;
     const bool jac = eo->jac != nullptr;
     if (jac && (!model->u_off || !model->u_item)) return CPE_E_NULL;
+    const int cfg = eval_cfg();
     EvalParams p;
     p.m = *model; p.b = *b; p.q = q; p.eo = *eo;
+    p.ea = exp(b->loss_a); p.eb = exp(b->loss_b); p.ec = exp(b->loss_c);
     p.TPF = b->C * 24;
-    int F = 288 / p.TPF;
+    const int budget = (cfg >= 2) ? 160 : 288;          // threads per CTA the frames are packed into
+    int F = budget / p.TPF;
     if (F < 1) F = 1;
     if (F > 4) F = 4;
     if (F > b->N) F = b->N;
@@ -316,17 +346,17 @@ static int launch_eval(const cpe_model *model, const cpe_batch *b, const double 
     const size_t smem = doubles * sizeof(double);
     int threads = ((F * p.TPF + 31) / 32) * 32;
     if (threads < 128) threads = 128;
-    cudaError_t e;
-    if (jac) {
-        e = cudaFuncSetAttribute(eval_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return (int)e;
-        eval_kernel<true><<<b->S * p.chunks, threads, smem, st>>>(p);
-    } else {
-        e = cudaFuncSetAttribute(eval_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return (int)e;
-        eval_kernel<false><<<b->S * p.chunks, threads, smem, st>>>(p);
+    const int grid = b->S * p.chunks;
+    if (threads > 160 || cfg < 2) {
+        if (cfg == 1) return jac ? launch_cfg<true, 288, 3>(p, grid, threads, smem, st)
+                                 : launch_cfg<false, 288, 3>(p, grid, threads, smem, st);
+        return jac ? launch_cfg<true, 288, 2>(p, grid, threads, smem, st)
+                   : launch_cfg<false, 288, 2>(p, grid, threads, smem, st);
     }
-    return (int)cudaGetLastError();
+    if (cfg == 3) return jac ? launch_cfg<true, 160, 6>(p, grid, threads, smem, st)
+                             : launch_cfg<false, 160, 6>(p, grid, threads, smem, st);
+    return jac ? launch_cfg<true, 160, 5>(p, grid, threads, smem, st)
+               : launch_cfg<false, 160, 5>(p, grid, threads, smem, st);
 }
 
 }  // namespace cpe

@@ -20,30 +20,40 @@ __device__ __forceinline__ void project_point(const double *X, const double *cam
     const double x = X[0] * R[0] + X[1] * R[1] + X[2] * R[2] + cam[17];
     const double y = X[0] * R[3] + X[1] * R[4] + X[2] * R[5] + cam[18];
     const double z = X[0] * R[6] + X[1] * R[7] + X[2] * R[8] + cam[19];
-    const double a = x / z, b = y / z;
-    const double r2 = a * a + b * b;
-    const double r = sqrt(r2);
-    double s, g = 0.0;
+    // two divisions per point: 1/z, then the reciprocals of r + 1e-12, 1 + r^2 and r from a single 1/(product)
+    double iz, s, g = 0.0, a, b;
     if (model == CPE_CAM_FISHEYE) {
+        const double izp = 1.0 / z;                         // a, b first (r depends on them)
+        a = x * izp; b = y * izp; iz = izp;
+        const double r2 = a * a + b * b;
+        const double r = sqrt(r2);
         const double th = atan(r);
         const double t2 = th * th;
         const double poly = 1.0 + t2 * (cam[4] + t2 * (cam[5] + t2 * (cam[6] + t2 * cam[7])));
         const double thd = th * poly;
         const double re = r + 1e-12;
-        s = thd / re;
         if (DERIV) {
+            const double rr = r > 0.0 ? r : 1.0;
+            const double p1 = re * (1.0 + r2);
+            const double inv = 1.0 / (p1 * rr);
+            const double ire = inv * (1.0 + r2) * rr, i1r2 = inv * re * rr, ir = inv * p1;
+            s = thd * ire;
             const double dpoly = 1.0 + t2 * (3.0 * cam[4] + t2 * (5.0 * cam[5] + t2 * (7.0 * cam[6] + t2 * 9.0 * cam[7])));
-            const double ds_dr = (dpoly / (1.0 + r2) * re - thd) / (re * re);
-            g = r > 0.0 ? ds_dr / r : 0.0;
+            const double ds_dr = (dpoly * i1r2 * re - thd) * (ire * ire);
+            g = r > 0.0 ? ds_dr * ir : 0.0;
+        } else {
+            s = thd / re;
         }
     } else {
+        iz = 1.0 / z;
+        a = x * iz; b = y * iz;
+        const double r2 = a * a + b * b;
         s = 1.0 + r2 * (cam[4] + r2 * (cam[5] + r2 * cam[6]));
         if (DERIV) g = 2.0 * cam[4] + r2 * (4.0 * cam[5] + 6.0 * r2 * cam[6]);
     }
     o.u = cam[0] * (a * s) + cam[2];
     o.v = cam[1] * (b * s) + cam[3];
     if (DERIV) {
-        const double iz = 1.0 / z;
         const double xa = s + a * a * g, xb = a * b * g, yb = s + b * b * g;
         // d(u)/d(Xc) and d(v)/d(Xc)
         const double ux = cam[0] * xa * iz, uy = cam[0] * xb * iz, uz = -cam[0] * (xa * a + xb * b) * iz;

@@ -206,7 +206,7 @@ def jacobian_pattern(chain_link=None):
 
     Returns (u_off[25], u_item[n_u], cols) where cols[l] lists the coordinate indices (into q[54]) of marker l's
     columns: base x,y,z then (phi,theta,psi) of every chain link.  Marker l owns 2*len(cols[l]) consecutive entries
-    of the 540-vector of one frame.view, starting at 2*(3*l + u_off[l]): the u row, then the v row."""
+    of the 540-vector of one frame.view, starting at 2*(3*l + u_off[l]): one (du/dq_j, dv/dq_j) pair per column."""
     if chain_link is None:
         lengths, radii, _ = animal("jules")
         chain_link, _ = marker_chains(lengths, radii)
@@ -233,8 +233,8 @@ def jacobian_to_dense(jac_packed, chain_link=None):
     for l in range(N_MARKERS):
         n = len(cols[l])
         o = 2 * (3 * l + int(u_off[l]))
-        out[..., l, 0, cols[l]] = jac_packed[..., o:o + n]
-        out[..., l, 1, cols[l]] = jac_packed[..., o + n:o + 2 * n]
+        out[..., l, 0, cols[l]] = jac_packed[..., o:o + 2 * n:2]
+        out[..., l, 1, cols[l]] = jac_packed[..., o + 1:o + 2 * n:2]
     return out
 
 

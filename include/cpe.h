@@ -115,9 +115,9 @@ typedef struct cpe_eval_out {
     double *c_eq;                   /* [S,N,26] */
     double *v_in;                   /* [S,N,n_ineq]  t - clamp(t, lo, up), t = d + lam/mu */
     double *jac;                    /* [S,N,C,2*(72+n_u)] packed chain-sparse d(u,v)/dq (540 per frame.view): marker l owns
-                                       2*ncol(l) entries at 2*(3l+u_off[l]), ncol = 3 + u_off[l+1]-u_off[l]: first the
-                                       u row then the v row, columns = base x,y,z then (phi,theta,psi) of each chain
-                                       link in chain order.  Independent of the hypothesis index w. */
+                                       2*ncol(l) entries at 2*(3l+u_off[l]), ncol = 3 + u_off[l+1]-u_off[l]: one
+                                       (du/dq_j, dv/dq_j) pair per column j, columns = base x,y,z then
+                                       (phi,theta,psi) of each chain link in chain order.  Independent of w. */
 } cpe_eval_out;
 
 /* Outputs of cpe_assemble: the per-frame reduced normal equations after Marquardt damping and elimination. */
