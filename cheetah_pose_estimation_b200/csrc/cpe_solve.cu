@@ -1,5 +1,5 @@
-// cpe_solve.cu -- K3: batched block-banded LDL^T solve of the reduced normal equations, K4: step application,
-// K5: step acceptance, plus the small reductions.  Replaces what IPOPT + MA97 do inside the reference's solver seam
+// cpe_solve.cu -- K4: step application, K5: step acceptance, plus the small reductions (K3, the block-banded
+// solve, lives in cpe_bandsolve.cu).  Replaces what IPOPT + MA97 do inside the reference's solver seam
 // (acinoset_opt.py:611-617; shared/physical_education/utils.py:459-548) for the Gauss-Newton/LM formulation.
 //
 // System per sequence (n = 28 independent coordinates per frame, block half-bandwidth 3 frames):
@@ -15,253 +15,6 @@
 #include "cpe.h"
 
 namespace cpe {
-
-constexpr int NB = CPE_N_IND;      // 28
-constexpr int LD = 29;             // padded leading dimension in shared memory (bank spread for column access)
-constexpr int BLK = NB * LD;
-constexpr int SOLVE_THREADS = 224; // 196 = 28 rows x 7 column-quads do the block algebra; warp 6 does the vectors
-
-__device__ __forceinline__ double stencil(int k, int j, int nf) {
-    const double c[4] = {-1.0, 3.0, -3.0, 1.0};
-    double s = 0.0;
-    for (int r = k - 3; r <= k - j; ++r) {
-        if (r < 0 || r > nf - 4) continue;
-        s += c[k - r] * c[k - j - r];
-    }
-    return s;
-}
-
-// out[r][c0..c0+3] -= sum_x X[r][x] * Y[c][x]   (out may be SUBTRACT = false -> overwrite with +sum)
-template <bool SUBTRACT>
-__device__ __forceinline__ void gemm_nt(double *out, const double *X, const double *Y, int r, int c0) {
-    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-    const double *xr = X + r * LD;
-    const double *y0 = Y + c0 * LD, *y1 = y0 + LD, *y2 = y1 + LD, *y3 = y2 + LD;
-#pragma unroll 7
-    for (int x = 0; x < NB; ++x) {
-        const double xv = xr[x];
-        a0 += xv * y0[x];
-        a1 += xv * y1[x];
-        a2 += xv * y2[x];
-        a3 += xv * y3[x];
-    }
-    double *o = out + r * LD + c0;
-    if (SUBTRACT) {
-        o[0] -= a0; o[1] -= a1; o[2] -= a2; o[3] -= a3;
-    } else {
-        o[0] = a0; o[1] = a1; o[2] = a2; o[3] = a3;
-    }
-}
-
-struct SolveParams {
-    cpe_batch b;
-    const double *wq;
-    const int32_t *ind_idx;
-    const double *S;
-    const double *ghat;
-    cpe_solve_io io;
-};
-
-__global__ void __launch_bounds__(SOLVE_THREADS) band_solve_kernel(const __grid_constant__ SolveParams p) {
-    extern __shared__ double sm[];
-    const int tid = threadIdx.x;
-    const int s = blockIdx.x;
-    const int N = p.b.N;
-    const int nf = p.b.n_frames[s];
-    double *buf[10];
-#pragma unroll
-    for (int i = 0; i < 10; ++i) buf[i] = sm + i * BLK;
-    double *wd = sm + 10 * BLK;          // [28]
-    double *wv = wd + 28;                // w_{k}, ring of 4 : [4][28]
-    double *uv = wv + 4 * 28;            // u_{k}, ring of 4 : [4][28]
-    double *dv = uv + 4 * 28;            // backward ring [4][28]
-    double *part = dv + 4 * 28;          // [3][28]
-    __shared__ int bad;
-    if (tid == 0) bad = 0;
-    const double h = p.b.h[s];
-    const double h4 = h * h * h * h;
-    if (tid < 28) wd[tid] = 2.0 * p.wq[p.ind_idx[tid]] / h4;
-    for (int i = tid; i < 12 * 28; i += SOLVE_THREADS) wv[i] = 0.0;
-    __syncthreads();
-
-    const bool alg = tid < 196;
-    const int r = tid / 7, c0 = (tid % 7) * 4;
-    // roles of the ten buffers (indices rotate each row)
-    int iW1a = 0, iW1b = 1, iW2a = 2, iPa = 3, iPb = 4, iPc = 5, iT2 = 6, iT1 = 7, iL2 = 8, iL1 = 9;
-    double *Lf = p.io.Lfac + (size_t)s * N * 4 * 784;
-    const double *Sg = p.S + (size_t)s * N * 784;
-    const double *gh = p.ghat + (size_t)s * N * 28;
-    double *zb = p.io.zbuf + (size_t)s * N * 28;
-
-    for (int k = 0; k < nf; ++k) {
-        double *W1a = buf[iW1a], *W1b = buf[iW1b], *W2a = buf[iW2a];
-        double *Pa = buf[iPa], *Pb = buf[iPb], *Pc = buf[iPc];
-        double *T2 = buf[iT2], *T1 = buf[iT1], *L2 = buf[iL2], *L1 = buf[iL1];
-        const double m0 = stencil(k, 0, nf), m1 = stencil(k, 1, nf), m2 = stencil(k, 2, nf), m3 = stencil(k, 3, nf);
-        double *Lk = Lf + (size_t)k * 4 * 784;
-        // ---- stage 1: L3 (to global), D init (into Pc), T2 ------------------------------------------------------
-        double dreg[4];
-        if (alg) {
-            const double wr = wd[r];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int c = c0 + i;
-                double d = Sg[(size_t)k * 784 + r * 28 + c] + (r == c ? m0 * wr : 0.0);
-                double l3 = 0.0;
-                if (k >= 3) {
-                    const double pc = Pc[r * LD + c];
-                    l3 = m3 * wr * pc;
-                    d -= m3 * m3 * wr * wd[c] * pc;       // T3 L3^T, P symmetric
-                }
-                Lk[2 * 784 + r * 28 + c] = l3;
-                dreg[i] = d;
-                double t2 = (r == c ? m2 * wr : 0.0);
-                if (k >= 3) t2 -= m3 * wr * W1b[c * LD + r];
-                T2[r * LD + c] = t2;
-            }
-        }
-        __syncthreads();
-        if (alg) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) Pc[r * LD + c0 + i] = dreg[i];     // D_k now lives in Pc
-        }
-        // ---- stage 2: L2 = T2 Pb ; T1 init ------------------------------------------------------------------------
-        if (alg) {
-            if (k >= 2) gemm_nt<false>(L2, T2, Pb, r, c0);
-            const double wr = wd[r];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int c = c0 + i;
-                double t1 = (r == c ? m1 * wr : 0.0);
-                if (k >= 3) t1 -= m3 * wr * W2a[c * LD + r];
-                T1[r * LD + c] = t1;
-                if (k < 2) L2[r * LD + c] = 0.0;
-            }
-        }
-        __syncthreads();
-        // ---- stage 3: T1 -= T2 W1a^T ; D -= T2 L2^T ----------------------------------------------------------------
-        if (alg && k >= 2) {
-            gemm_nt<true>(T1, T2, W1a, r, c0);
-            gemm_nt<true>(Pc, T2, L2, r, c0);
-        }
-        __syncthreads();
-        // ---- stage 4: L1 = T1 Pa -------------------------------------------------------------------------------------
-        if (alg) {
-            if (k >= 1) {
-                gemm_nt<false>(L1, T1, Pa, r, c0);
-            } else {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) L1[r * LD + c0 + i] = 0.0;
-            }
-        }
-        __syncthreads();
-        // ---- stage 5: D -= T1 L1^T ; store L1, L2 ; forward substitution on warp 6 ----------------------------------
-        if (alg) {
-            if (k >= 1) gemm_nt<true>(Pc, T1, L1, r, c0);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                Lk[0 * 784 + r * 28 + c0 + i] = L1[r * LD + c0 + i];
-                Lk[1 * 784 + r * 28 + c0 + i] = L2[r * LD + c0 + i];
-            }
-        } else {
-            const int rr = tid - 196;
-            // w_k = -ghat_k - L1 w_{k-1} - L2 w_{k-2} - m3 Wd u_{k-3}
-            double acc = -gh[(size_t)k * 28 + rr];
-            const double *w1 = wv + ((k + 3) & 3) * 28, *w2 = wv + ((k + 2) & 3) * 28;
-            const double *u3 = uv + ((k + 1) & 3) * 28;
-            if (k >= 1)
-                for (int x = 0; x < 28; ++x) acc -= L1[rr * LD + x] * w1[x];
-            if (k >= 2)
-                for (int x = 0; x < 28; ++x) acc -= L2[rr * LD + x] * w2[x];
-            if (k >= 3) acc -= m3 * wd[rr] * u3[rr];
-            wv[(k & 3) * 28 + rr] = acc;
-        }
-        __syncthreads();
-        // ---- stage 6: P_k = D_k^-1 by in-place Gauss-Jordan --------------------------------------------------------
-        double *D = Pc;
-        for (int pv = 0; pv < NB; ++pv) {
-            double f = 0.0, piv = 1.0, rowp[4] = {0, 0, 0, 0};
-            if (alg) {
-                f = D[r * LD + pv];
-                piv = D[pv * LD + pv];
-#pragma unroll
-                for (int i = 0; i < 4; ++i) rowp[i] = D[pv * LD + c0 + i];
-            }
-            __syncthreads();
-            if (alg) {
-                if (!(piv > 0.0)) {
-                    if (r == pv && c0 == 0) bad = 1;
-                    piv = (piv == 0.0 || piv != piv) ? 1e-300 : piv;
-                }
-                const double ip = 1.0 / piv;
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int c = c0 + i;
-                    double v;
-                    if (r == pv) v = (c == pv) ? ip : rowp[i] * ip;
-                    else v = (c == pv) ? -f * ip : D[r * LD + c] - f * rowp[i] * ip;
-                    D[r * LD + c] = v;
-                }
-            }
-            __syncthreads();
-        }
-        // symmetrise, store P_k, u_k = P_k w_k
-        double sym[4];
-        if (alg) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) sym[i] = 0.5 * (D[r * LD + c0 + i] + D[(c0 + i) * LD + r]);
-        }
-        __syncthreads();
-        if (alg) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                D[r * LD + c0 + i] = sym[i];
-                Lk[3 * 784 + r * 28 + c0 + i] = sym[i];
-            }
-        }
-        __syncthreads();
-        if (!alg) {
-            const int rr = tid - 196;
-            const double *wk = wv + (k & 3) * 28;
-            double acc = 0.0;
-            for (int x = 0; x < 28; ++x) acc += D[rr * LD + x] * wk[x];
-            uv[(k & 3) * 28 + rr] = acc;
-            zb[(size_t)k * 28 + rr] = acc;
-        }
-        __syncthreads();
-        // rotate roles: new W1a = L1, W1b = old W1a, W2a = L2, Pa = D(Pc), Pb = old Pa, Pc = old Pb; the rest is scratch
-        const int nW1a = iL1, nW1b = iW1a, nW2a = iL2, nPa = iPc, nPb = iPa, nPc = iPb;
-        const int f0 = iW1b, f1 = iW2a, f2 = iT2, f3 = iT1;
-        iW1a = nW1a; iW1b = nW1b; iW2a = nW2a; iPa = nPa; iPb = nPb; iPc = nPc;
-        iT2 = f0; iT1 = f1; iL2 = f2; iL1 = f3;
-    }
-    // ---- backward: d_k = u_k - L1(k+1)^T d_{k+1} - L2(k+2)^T d_{k+2} - L3(k+3)^T d_{k+3} ----------------------------
-    for (int i = tid; i < 4 * 28; i += SOLVE_THREADS) dv[i] = 0.0;
-    __syncthreads();
-    double *dout = p.io.delta_ind + (size_t)s * N * 28;
-    for (int k = nf - 1; k >= 0; --k) {
-        if (tid < 84) {
-            const int j = tid / 28, c = tid - j * 28;     // block offset j+1
-            const int kk = k + j + 1;
-            double acc = 0.0;
-            if (kk < nf) {
-                const double *Lb = Lf + ((size_t)kk * 4 + j) * 784 + c;
-                const double *dk = dv + (kk & 3) * 28;
-#pragma unroll 7
-                for (int x = 0; x < 28; ++x) acc += Lb[x * 28] * dk[x];
-            }
-            part[tid] = acc;
-        }
-        __syncthreads();
-        if (tid < 28) {
-            const double d = zb[(size_t)k * 28 + tid] - part[tid] - part[28 + tid] - part[56 + tid];
-            dv[(k & 3) * 28 + tid] = d;
-            dout[(size_t)k * 28 + tid] = d;
-        }
-        __syncthreads();
-    }
-    if (tid == 0 && p.io.status) p.io.status[s] = bad;
-}
 
 // ---- K4: back-substitute eliminated coords, q_try = q + delta, predicted reduction -----------------------------
 struct ApplyParams {
@@ -402,23 +155,6 @@ extern "C" int cpe_version(void) { return CPE_VERSION; }
 extern "C" int cpe_reduce_cost_f64(const cpe_batch *b, const double *frame_cost, double *cost, void *stream) {
     if (!b || !frame_cost || !cost) return CPE_E_NULL;
     cpe::reduce_cost_kernel<<<(b->S + 3) / 4, 128, 0, (cudaStream_t)stream>>>(b->S, b->N, b->n_frames, frame_cost, cost);
-    return (int)cudaGetLastError();
-}
-
-extern "C" int cpe_band_solve_f64(const cpe_model *model, const cpe_batch *b, const double *Sblk, const double *ghat,
-                                  const cpe_solve_io *io, void *stream) {
-    if (!model || !b || !Sblk || !ghat || !io || !io->Lfac || !io->zbuf || !io->delta_ind) return CPE_E_NULL;
-    cpe::SolveParams p;
-    p.b = *b;
-    p.wq = model->wq;
-    p.ind_idx = model->ind_idx;
-    p.S = Sblk;
-    p.ghat = ghat;
-    p.io = *io;
-    const size_t smem = (size_t)(10 * cpe::BLK + 28 + 12 * 28 + 3 * 28) * sizeof(double);
-    cudaError_t e = cudaFuncSetAttribute(cpe::band_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return (int)e;
-    cpe::band_solve_kernel<<<b->S, cpe::SOLVE_THREADS, smem, (cudaStream_t)stream>>>(p);
     return (int)cudaGetLastError();
 }
 

@@ -150,7 +150,7 @@ class Solver:
             self.y = torch.zeros(S, N, G, 6, **f64)
             self.g = torch.zeros(S, N, 54, **f64)
             self.diagH = torch.zeros(S, N, 54, **f64)
-            self.Lfac = torch.empty(S, N, 4, 28, 28, **f64)
+            self.Lfac = torch.empty(S, N, 3, 28, 28, **f64)
             self.zbuf = torch.zeros(S, N, 28, **f64)
             self.delta_ind = torch.zeros(S, N, 28, **f64)
             self.status = torch.zeros(S, dtype=torch.int32, device=dev)

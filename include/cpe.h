@@ -133,7 +133,7 @@ typedef struct cpe_assemble_out {
 
 /* Workspace + outputs of the block-banded solve. */
 typedef struct cpe_solve_io {
-    double *Lfac;                   /* [S,N,4,28,28] workspace: L1,L2,L3 (unit-lower block factors) and P = D^-1 */
+    double *Lfac;                   /* [S,N,3,28,28] workspace: L1, L2, L3 (unit-lower block factors of each block row) */
     double *zbuf;                   /* [S,N,28] workspace */
     double *delta_ind;              /* [S,N,28] out */
     int32_t *status;                /* [S] out: 0 ok, 1 non-positive pivot encountered */
