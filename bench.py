@@ -339,21 +339,19 @@ def main():
     import torch.distributed as dist
     r = run_b200(a)
     world, rank = r["world"], r["rank"]
-    # max over ranks of the device-timed regions
-    t = torch.tensor([r["ms"], r["e2e"][0] if r["e2e"] else 0.0, r["kern_ms"] / max(1, r["n_kern"])],
-                     dtype=torch.float64, device=r["dev"])
+    # max over ranks of the device-timed regions; the path's only collective: the final cost/statistics reduce
+    from cheetah_pose_estimation_b200 import sharding
+    ms = sharding.reduce_max(r["ms"], r["dev"])
+    e2e_ms = sharding.reduce_max(r["e2e"][0] if r["e2e"] else 0.0, r["dev"])
+    kern_ms = sharding.reduce_max(r["kern_ms"] / max(1, r["n_kern"]), r["dev"])
     stats = torch.cat([r["cost_sum"], torch.tensor([float(r["launches"])], dtype=torch.float64, device=r["dev"])])
     if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(stats, op=dist.ReduceOp.SUM)       # the path's only collective: final cost/statistics reduce
-    ms, e2e_ms, kern_ms = t.tolist()
+        dist.all_reduce(stats, op=dist.ReduceOp.SUM)
     lm = lm_leg(a, r)
     if world > 1 and lm is not None:
-        v = torch.tensor([lm["ms"]], dtype=torch.float64, device=r["dev"])
-        dist.all_reduce(v, op=dist.ReduceOp.MAX)
+        lm["ms"] = sharding.reduce_max(lm["ms"], r["dev"])
         lm["sequences"] *= world
-        lm["sequences_per_s"] = lm["sequences"] / (v.item() * 1e-3)
-        lm["ms"] = v.item()
+        lm["sequences_per_s"] = lm["sequences"] / (lm["ms"] * 1e-3)
     if rank == 0:
         fv_rank = a.seqs * a.frames * a.cams
         fv_total = fv_rank * world

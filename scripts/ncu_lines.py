@@ -40,7 +40,7 @@ for cubin in glob.glob(os.path.join(tmp, "*.cubin")):
                 if m:
                     line = (os.path.basename(m.group(1)), int(m.group(2)))
                     continue
-                if re.match(r"\s+/\*[0-9a-f]{4}\*/", ln):
+                if re.match(r"\s+/\*[0-9a-f]{4,}\*/", ln):
                     seq.append(line)
             if len(seq) == len(blk["rows"]):
                 lines = seq
