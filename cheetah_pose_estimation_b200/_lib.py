@@ -15,13 +15,14 @@ c_f64p = C.c_void_p
 
 class CpeModel(C.Structure):
     _fields_ = [
-        ("n_ineq", C.c_int32), ("n_blocks", C.c_int32), ("n_groups", C.c_int32), ("n_blk_items", C.c_int32),
-        ("n_u", C.c_int32), ("reserved_", C.c_int32),
-        ("chain_link", c_i32p), ("slot_of", c_i32p), ("eq_pairs", c_i32p), ("ineq_idx", c_i32p),
+        ("n_ineq", C.c_int32), ("n_groups", C.c_int32), ("n_u", C.c_int32), ("n_ent", C.c_int32),
+        ("chain_link", c_i32p), ("eq_pairs", c_i32p), ("ineq_idx", c_i32p),
         ("ineq_bounds", c_f64p), ("wq", c_f64p), ("meas_w", c_f64p), ("ind_idx", c_i32p), ("ind_pos", c_i32p),
-        ("blk_nodes", c_i32p), ("blk_id", c_i32p), ("blk_item_ptr", c_i32p), ("blk_items", c_i32p),
-        ("blk_eq_ptr", c_i32p), ("blk_eq_items", c_i32p), ("grp_ndep", c_i32p), ("grp_nnb", c_i32p),
-        ("grp_dep", c_i32p), ("grp_nb", c_i32p), ("grp_nbpos", c_i32p), ("u_off", c_i32p), ("u_item", c_i32p),
+        ("grp_ndep", c_i32p), ("grp_nnb", c_i32p), ("grp_dep", c_i32p), ("grp_nb", c_i32p),
+        ("u_off", c_i32p), ("u_item", c_i32p),
+        ("ent_pq", c_i32p), ("a_ptr", c_i32p), ("a_items", c_i32p), ("e_ptr", c_i32p), ("e_items", c_i32p),
+        ("i_ptr", c_i32p), ("i_items", c_i32p), ("diag_ent", c_i32p), ("grad_ent", c_i32p), ("grp_src", c_i32p),
+        ("s_src", c_i32p), ("s_ptr", c_i32p), ("s_items", c_i32p),
     ]
 
 

@@ -1,0 +1,397 @@
+// cpe_assemble.cu -- K2: fused residual + forward-mode Jacobian + J^T J / J^T r accumulation in the tree-sparse
+// pattern of the skeleton, augmented-Lagrangian rows, Marquardt damping and the per-frame Schur elimination of the
+// 26 coordinates that carry no motion prior.  The Jacobian is never materialised.
+//
+// Reference arithmetic being replaced: what ASL evaluates inside `ipopt` (gradient / Hessian of the objective and
+// constraints of acinoset_opt.py:601-618) for the terms of
+//   acinoset_misc.py:278-288, 459-484, 2001-2015 (measurement), :639-677 (motion), system.py:574-586 (joints),
+//   cheetah.py:306-352 (inequalities).
+//
+// Mapping (sm_100a, FP64): one CTA per frame.  Front end as K1 (sincos -> R -> marker positions, chain derivative
+// vectors U).  One thread per (camera, marker) projects, weights by the IRLS curvature max(rho'/E, 0) and leaves a
+// 3x3 + 3 block; blocks are summed over cameras (fixed order) into A_l, b_l.  Every nonzero of the frame Hessian
+// H = sum_l G_l^T A_l G_l (+ mu Jc^T Jc + active inequality rows) and of the gradient is then ONE gather over a
+// static item list built on the host (skeleton.assemble_tables): no atomics, no index arithmetic in the kernel.
+// The five elimination groups are reduced by one warp each, Gauss-Jordan in registers with warp shuffles
+// (lane = tableau column), and the reduced 28x28 block S and ghat are gathered the same way.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+
+#include "cpe.h"
+#include "cpe_internal.cuh"
+
+namespace cpe {
+
+struct AsmParams {
+    cpe_model m;
+    cpe_batch b;
+    const double *q;
+    const double *damp;
+    cpe_assemble_out ao;
+    int TPF;        // C * 24
+    int at_size;    // doubles of the aliased region (per-task blocks, then entries + group scratch)
+    double ea, eb, ec;
+};
+
+// per-frame shared layout (doubles), after cam[C*24]
+constexpr int A_QO = 0, A_SCO = 56, A_RO = 160, A_POSO = 314, A_GV = 386, A_BV = 1056, A_EQG = 2004, A_EQR = 2160,
+              A_VIN = 2186, A_MOG = 2218, A_DIAG = 2272, A_AT = 2326;
+constexpr int G_U0 = 10, B_U0 = 216, B_G0 = 876, GRAD_Q = 63;       // must match skeleton.py
+constexpr int ENT_PAD = 640, DDI_SZ = CPE_MAX_GROUPS * 72, YS_SZ = CPE_MAX_GROUPS * 78;
+
+__device__ __forceinline__ double motion_m0(int k, int nf) {
+    const double c[4] = {-1.0, 3.0, -3.0, 1.0};
+    double s = 0.0;
+    for (int r = k - 3; r <= k; ++r) {
+        if (r < 0 || r > nf - 4) continue;
+        s += c[k - r] * c[k - r];
+    }
+    return s;
+}
+
+template <int MAXT, int MINB>
+__global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_constant__ AsmParams p) {
+    extern __shared__ __align__(16) double sm[];
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const int N = p.b.N, C = p.b.C, W = p.b.W, TPF = p.TPF;
+    const int s = blockIdx.y, k = blockIdx.x;
+    const int nf = p.b.n_frames[s];
+    if (k >= nf) return;
+    const size_t fidx = (size_t)s * N + k;
+    const int n_ineq = p.m.n_ineq, n_u = p.m.n_u, n_ent = p.m.n_ent;
+    double *cam = sm;
+    double *fr = sm + C * CPE_CAM_STRIDE;
+    double *GV = fr + A_GV, *BV = fr + A_BV, *AT = fr + A_AT;
+    double *ENT = AT, *DDI = AT + ENT_PAD, *YS = DDI + DDI_SZ;
+
+    const bool mvalid = tid < TPF;
+    const int mc = tid / 24, ml = tid - mc * 24;
+    const size_t midx0 = ((fidx * C + mc) * 24 + ml) * W;
+    float4 m4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    double4 m8 = make_double4(0.0, 0.0, 0.0, 0.0);
+    const bool m64 = p.b.meas_is_f64 != 0;
+    if (mvalid) {
+        if (m64) m8 = reinterpret_cast<const double4 *>(p.b.meas)[midx0];
+        else m4 = __ldg(reinterpret_cast<const float4 *>(p.b.meas) + midx0);
+    }
+    const double *qf = p.q + fidx * 54;
+    for (int c = tid; c < 54; c += nt) fr[A_QO + c] = qf[c];
+    for (int i = tid; i < C * CPE_CAM_STRIDE; i += nt) cam[i] = p.b.cams[(size_t)s * C * CPE_CAM_STRIDE + i];
+    if (tid < 10) GV[tid] = (tid == 0 || tid == 4 || tid == 8) ? 1.0 : 0.0;      // identity columns e_x, e_y, e_z
+    __syncthreads();
+    for (int a = tid; a < 51; a += nt) sincos(fr[A_QO + 3 + a], &fr[A_SCO + 2 * a], &fr[A_SCO + 2 * a + 1]);
+    __syncthreads();
+    for (int link = tid; link < 17; link += nt) rot_from_sc(fr + A_SCO + 6 * link, fr + A_RO + 9 * link);
+    __syncthreads();
+
+    // ---- camera-independent items: positions, U, joint rows, inequality rows, motion gradient --------------------
+    const double h = p.b.h[s];
+    const double mu_eq = p.b.mu_eq, mu_in = p.b.mu_in;
+    {
+        const double *cvec = p.b.chain_vec + (size_t)s * 24 * CPE_MAX_CHAIN * 3;
+        const int32_t *chain_link = p.m.chain_link;
+        const int n_items = 24 + n_u + 26 + n_ineq + 54;
+        for (int it0 = tid; it0 < n_items; it0 += nt) {
+            int it = it0;
+            if (it < 24) {
+                const int l = it;
+                double x = fr[A_QO + 0], y = fr[A_QO + 1], z = fr[A_QO + 2];
+#pragma unroll
+                for (int j = 0; j < CPE_MAX_CHAIN; ++j) {
+                    const int link = chain_link[l * CPE_MAX_CHAIN + j];
+                    if (link >= 0) {
+                        const double *Rl = fr + A_RO + link * 9;
+                        const double *v = cvec + (l * CPE_MAX_CHAIN + j) * 3;
+                        const double v0 = v[0], v1 = v[1], v2 = v[2];
+                        x += Rl[0] * v0 + Rl[1] * v1 + Rl[2] * v2;
+                        y += Rl[3] * v0 + Rl[4] * v1 + Rl[5] * v2;
+                        z += Rl[6] * v0 + Rl[7] * v1 + Rl[8] * v2;
+                    }
+                }
+                fr[A_POSO + l * 3 + 0] = x; fr[A_POSO + l * 3 + 1] = y; fr[A_POSO + l * 3 + 2] = z;
+                continue;
+            }
+            it -= 24;
+            if (it < n_u) {
+                const int code = p.m.u_item[it];
+                const int l = code >> 8, j = (code >> 4) & 15, a = code & 15;
+                const int link = chain_link[l * CPE_MAX_CHAIN + j];
+                const double *v = cvec + (l * CPE_MAX_CHAIN + j) * 3;
+                drot_times(fr + A_SCO + 6 * link, a, v[0], v[1], v[2], GV + G_U0 + 10 * (it / 3) + 3 * a);
+                continue;
+            }
+            it -= n_u;
+            if (it < 26) {
+                const int e = it;
+                const int4 pr4 = reinterpret_cast<const int4 *>(p.m.eq_pairs)[e];
+                const int la = pr4.x, lb = pr4.y, ia = pr4.z, ib = pr4.w;
+                const double *Ra = fr + A_RO + la * 9, *Rb = fr + A_RO + lb * 9;
+                const double a0 = Ra[ia], a1 = Ra[3 + ia], a2 = Ra[6 + ia];
+                const double b0 = Rb[ib], b1 = Rb[3 + ib], b2 = Rb[6 + ib];
+                const double c = a0 * b0 + a1 * b1 + a2 * b2;
+                const double lam = p.b.lam_eq ? p.b.lam_eq[fidx * 26 + e] : 0.0;
+                fr[A_EQR + e] = mu_eq * (c + lam / mu_eq);
+                // d c / d angles: (dR_a/dangle e_ia) . (R_b e_ib) and (R_a e_ia) . (dR_b/dangle e_ib)
+                const double ea0 = ia == 0, ea1 = ia == 1, ea2 = ia == 2;
+                const double eb0 = ib == 0, eb1 = ib == 1, eb2 = ib == 2;
+#pragma unroll
+                for (int x = 0; x < 3; ++x) {
+                    double d[3];
+                    drot_times(fr + A_SCO + 6 * la, x, ea0, ea1, ea2, d);
+                    fr[A_EQG + e * 6 + x] = d[0] * b0 + d[1] * b1 + d[2] * b2;
+                    drot_times(fr + A_SCO + 6 * lb, x, eb0, eb1, eb2, d);
+                    fr[A_EQG + e * 6 + 3 + x] = a0 * d[0] + a1 * d[1] + a2 * d[2];
+                }
+                continue;
+            }
+            it -= 26;
+            if (it < n_ineq) {
+                const int j = it;
+                const int ip = p.m.ineq_idx[2 * j], im = p.m.ineq_idx[2 * j + 1];
+                const double lo = p.m.ineq_bounds[2 * j], up = p.m.ineq_bounds[2 * j + 1];
+                const double d = fr[A_QO + ip] - (im >= 0 ? fr[A_QO + im] : 0.0);
+                const double lam = p.b.lam_in ? p.b.lam_in[fidx * n_ineq + j] : 0.0;
+                const double t = d + lam / mu_in;
+                fr[A_VIN + j] = t - fmin(fmax(t, lo), up);
+                continue;
+            }
+            it -= n_ineq;
+            {
+                const int c = it;
+                const double w = p.m.wq[c];
+                double val = 0.0;
+                if (w != 0.0) {
+                    // motion gradient: 2 w / h^2 * sum_r coef[k-r] d3_r, rows r = k-3..k within [0, nf-4]
+                    const double cf[4] = {-1.0, 3.0, -3.0, 1.0};
+                    double acc = 0.0;
+                    for (int r = k - 3; r <= k; ++r) {
+                        if (r < 0 || r > nf - 4) continue;
+                        const double *qr = p.q + ((size_t)s * N + r) * 54 + c;
+                        const double d3 = (qr[162] - 3.0 * qr[108] + 3.0 * qr[54] - qr[0]) / (h * h);
+                        acc += cf[k - r] * d3;
+                    }
+                    val = 2.0 * w / (h * h) * acc;
+                }
+                fr[A_MOG + c] = val;
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- one thread per (camera, marker): projection + IRLS-weighted 3x3 block and gradient 3-vector -------------
+    if (mvalid) {
+        const double la_ = p.b.loss_a, lb_ = p.b.loss_b, lc_ = p.b.loss_c;
+        const double *cm = cam + mc * CPE_CAM_STRIDE;
+        Proj pr;
+        project_point<true>(fr + A_POSO + ml * 3, cm, p.b.cam_model, pr);
+        const double cmult = cm[20];
+        double hu = 0.0, hv = 0.0, gu = 0.0, gv = 0.0;
+        for (int w = 0; w < W; ++w) {
+            double um, vm, gate;
+            if (w > 0) {
+                if (m64) m8 = reinterpret_cast<const double4 *>(p.b.meas)[midx0 + w];
+                else m4 = __ldg(reinterpret_cast<const float4 *>(p.b.meas) + midx0 + w);
+            }
+            if (m64) { um = m8.x; vm = m8.y; gate = m8.z; }
+            else { um = (double)m4.x; vm = (double)m4.y; gate = (double)m4.z; }
+            const double wgt = gate * p.m.meas_w[w * 24 + ml] * cmult;
+            const double eu = wgt * (pr.u - um), ev = wgt * (pr.v - vm);
+            const double Eu = fabs(eu), Ev = fabs(ev);
+            double rho, du_, dv_;
+            redescending(Eu, la_, lb_, lc_, p.ea, p.eb, p.ec, rho, du_);
+            redescending(Ev, la_, lb_, lc_, p.ea, p.eb, p.ec, rho, dv_);
+            gu += du_ * (eu > 0.0 ? 1.0 : (eu < 0.0 ? -1.0 : 0.0)) * wgt;
+            gv += dv_ * (ev > 0.0 ? 1.0 : (ev < 0.0 ? -1.0 : 0.0)) * wgt;
+            hu += (Eu > 0.0 ? fmax(du_ / Eu, 0.0) : 0.0) * wgt * wgt;
+            hv += (Ev > 0.0 ? fmax(dv_ / Ev, 0.0) : 0.0) * wgt * wgt;
+        }
+        double *ab = AT + tid * 9;
+        ab[0] = hu * pr.du[0] * pr.du[0] + hv * pr.dv[0] * pr.dv[0];
+        ab[1] = hu * pr.du[0] * pr.du[1] + hv * pr.dv[0] * pr.dv[1];
+        ab[2] = hu * pr.du[0] * pr.du[2] + hv * pr.dv[0] * pr.dv[2];
+        ab[3] = hu * pr.du[1] * pr.du[1] + hv * pr.dv[1] * pr.dv[1];
+        ab[4] = hu * pr.du[1] * pr.du[2] + hv * pr.dv[1] * pr.dv[2];
+        ab[5] = hu * pr.du[2] * pr.du[2] + hv * pr.dv[2] * pr.dv[2];
+        ab[6] = gu * pr.du[0] + gv * pr.dv[0];
+        ab[7] = gu * pr.du[1] + gv * pr.dv[1];
+        ab[8] = gu * pr.du[2] + gv * pr.dv[2];
+    }
+    __syncthreads();
+    // ---- A_l = sum over cameras (fixed order), expanded to full 3x3 columns in B space; b_l ------------------------
+    for (int i = tid; i < 216; i += nt) {
+        const int l = i / 9, comp = i - l * 9;
+        double v = 0.0;
+        for (int c = 0; c < C; ++c) v += AT[(c * 24 + l) * 9 + comp];
+        if (comp >= 6) {
+            BV[B_G0 + 3 * l + comp - 6] = v;
+        } else {
+            const int ri = comp < 3 ? 0 : (comp < 5 ? 1 : 2);
+            const int ci = comp < 3 ? comp : (comp < 5 ? comp - 2 : 2);
+            BV[9 * l + 3 * ci + ri] = v;
+            BV[9 * l + 3 * ri + ci] = v;
+        }
+    }
+    __syncthreads();
+    // ---- B = A_l U for every chain column ------------------------------------------------------------------------------
+    for (int it = tid; it < n_u; it += nt) {
+        const int l = p.m.u_item[it] >> 8;
+        const int o = 10 * (it / 3) + 3 * (it % 3);
+        const double *Al = BV + 9 * l;
+        const double u0 = GV[G_U0 + o], u1 = GV[G_U0 + o + 1], u2 = GV[G_U0 + o + 2];
+        BV[B_U0 + o + 0] = Al[0] * u0 + Al[3] * u1 + Al[6] * u2;
+        BV[B_U0 + o + 1] = Al[1] * u0 + Al[4] * u1 + Al[7] * u2;
+        BV[B_U0 + o + 2] = Al[2] * u0 + Al[5] * u1 + Al[8] * u2;
+    }
+    __syncthreads();
+    // ---- every Hessian / gradient nonzero = one gather over its static item list -------------------------------------
+    for (int e = tid; e < n_ent; e += nt) {
+        const int pq = p.m.ent_pq[e];
+        const int pp = pq >> 6, qq = pq & 63;
+        const bool grad = qq == GRAD_Q;
+        double acc = 0.0;
+        for (int i = p.m.a_ptr[e], i1 = p.m.a_ptr[e + 1]; i < i1; ++i) {
+            const int it = p.m.a_items[i];
+            const double *g = GV + (it >> 16), *b = BV + (it & 0xFFFF);
+            acc += g[0] * b[0] + g[1] * b[1] + g[2] * b[2];
+        }
+        double acce = 0.0;
+        for (int i = p.m.e_ptr[e], i1 = p.m.e_ptr[e + 1]; i < i1; ++i) {
+            const int it = p.m.e_items[i];
+            const double gi = fr[A_EQG + (it >> 8)];
+            acce += gi * (grad ? fr[A_EQR + (it & 255)] : mu_eq * fr[A_EQG + (it & 255)]);
+        }
+        double acci = 0.0;
+        for (int i = p.m.i_ptr[e], i1 = p.m.i_ptr[e + 1]; i < i1; ++i) {
+            const int it = p.m.i_items[i];
+            const double v = fr[A_VIN + (it >> 1)];
+            const double val = grad ? v : (v != 0.0 ? 1.0 : 0.0);
+            acci += (it & 1) ? -val : val;
+        }
+        acc += acce + mu_in * acci;
+        if (grad) {
+            acc += fr[A_MOG + pp];
+            if (p.ao.g) p.ao.g[fidx * 54 + pp] = acc;
+        } else if (p.ao.Hraw) {
+            double *o = p.ao.Hraw + fidx * 54 * 54;
+            o[pp * 54 + qq] = acc;
+            o[qq * 54 + pp] = acc;
+        }
+        ENT[e] = acc;
+    }
+    __syncthreads();
+    const double h4 = h * h * h * h;
+    if (tid < 54) {
+        const double d = ENT[p.m.diag_ent[tid]] + motion_m0(k, nf) * 2.0 * p.m.wq[tid] / h4;
+        fr[A_DIAG + tid] = d;
+        if (p.ao.diagH) p.ao.diagH[fidx * 54 + tid] = d;
+    }
+    if (!p.ao.S) return;
+    __syncthreads();
+
+    // ---- per-frame elimination of the dependent coordinates: one warp per group, tableau column per lane ----------
+    const double damp = p.damp[s];
+    constexpr int GD = CPE_GRP_MAX_DEP, GN = CPE_GRP_MAX_NB, TW = GD + GN + 1;
+    const int lane = tid & 31, wid = tid >> 5, nw = nt >> 5;
+    const int n_groups = p.m.n_groups;
+    for (int g = wid; g < n_groups; g += nw) {
+        double t[GD];
+        const int32_t *src = p.m.grp_src + g * GD * TW;
+#pragma unroll
+        for (int i = 0; i < GD; ++i) {
+            double v = 0.0;
+            if (lane < TW) {
+                const int si = src[i * TW + lane];
+                v = si == -2 ? 1.0 : (si < 0 ? 0.0 : ENT[si]);
+                if (lane == i && si >= 0) v += damp * fr[A_DIAG + p.m.grp_dep[g * GD + i]];
+            }
+            t[i] = v;
+            if (lane >= GD && lane < GD + GN) DDI[(g * GD + i) * GN + lane - GD] = v;
+        }
+#pragma unroll
+        for (int pc = 0; pc < GD; ++pc) {
+            const double piv = __shfl_sync(0xffffffffu, t[pc], pc);
+            const double prow = t[pc] * (1.0 / piv);
+#pragma unroll
+            for (int i = 0; i < GD; ++i) {
+                if (i == pc) continue;
+                const double f = __shfl_sync(0xffffffffu, t[i], pc);
+                t[i] -= f * prow;
+            }
+            t[pc] = prow;
+        }
+        // lanes GD..GD+GN-1 hold Y = Hdd^-1 Hdi (column lane-GD), lane GD+GN holds y = Hdd^-1 g_d
+        if (lane >= GD && lane < TW) {
+            const int j = lane - GD;
+#pragma unroll
+            for (int i = 0; i < GD; ++i) {
+                YS[(g * GD + i) * (GN + 1) + j] = t[i];
+                if (j < GN) p.ao.Y[((fidx * n_groups + g) * GD + i) * GN + j] = t[i];
+                else p.ao.y[(fidx * n_groups + g) * GD + i] = t[i];
+            }
+        }
+    }
+    __syncthreads();
+    // ---- reduced block S = H_ii + damping - sum_g Hdi^T Y and ghat = g_i - sum_g Hdi^T y (static gather) ----------------
+    double *So = p.ao.S + fidx * 784;
+    for (int e = tid; e < 28 * 29; e += nt) {
+        const int r = e / 29, c = e - r * 29;
+        double v;
+        if (c == 28) {
+            v = ENT[p.m.grad_ent[p.m.ind_idx[r]]];
+        } else {
+            const int si = p.m.s_src[r * 28 + c];
+            v = si >= 0 ? ENT[si] : 0.0;
+            if (r == c) v += damp * fr[A_DIAG + p.m.ind_idx[r]];
+        }
+        for (int i = p.m.s_ptr[e], i1 = p.m.s_ptr[e + 1]; i < i1; ++i) {
+            const int it = p.m.s_items[i];
+            const int g = it >> 8, a = (it >> 4) & 15, b = it & 15;
+            const double *D = DDI + g * GD * GN + a;
+            const double *Yc = YS + g * GD * (GN + 1) + (b == 15 ? GN : b);
+            double sacc = 0.0;
+#pragma unroll
+            for (int ii = 0; ii < GD; ++ii) sacc += D[ii * GN] * Yc[ii * (GN + 1)];
+            v -= sacc;
+        }
+        if (c == 28) p.ao.ghat[fidx * 28 + r] = v;
+        else So[r * 28 + c] = v;
+    }
+}
+
+template <int MAXT, int MINB>
+static int launch_asm(const AsmParams &p, dim3 grid, int threads, size_t smem, cudaStream_t st) {
+    cudaError_t e = cudaFuncSetAttribute(assemble_kernel<MAXT, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    assemble_kernel<MAXT, MINB><<<grid, threads, smem, st>>>(p);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace cpe
+
+extern "C" int cpe_assemble_f64(const cpe_model *model, const cpe_batch *b, const double *q, const double *damp,
+                                const cpe_assemble_out *out, void *stream) {
+    using namespace cpe;
+    if (!model || !b || !q || !out) return CPE_E_NULL;
+    if (b->S <= 0 || b->N <= 0 || b->C <= 0 || b->C > CPE_MAX_CAMS || (b->W != 1 && b->W != 3)) return CPE_E_DIM;
+    if (b->S > 65535 || model->n_ineq > CPE_MAX_INEQ || model->n_groups > CPE_MAX_GROUPS) return CPE_E_DIM;
+    if (model->n_u != 198 || model->n_ent <= 0 || model->n_ent > ENT_PAD) return CPE_E_DIM;
+    if (!model->ent_pq || !model->a_ptr || !model->a_items || !model->e_ptr || !model->e_items || !model->i_ptr ||
+        !model->i_items || !model->diag_ent || !model->grad_ent || !model->grp_src || !model->s_src || !model->s_ptr ||
+        !model->s_items)
+        return CPE_E_NULL;
+    if (out->S && (!damp || !out->ghat || !out->Y || !out->y)) return CPE_E_NULL;
+    AsmParams p;
+    p.m = *model; p.b = *b; p.q = q; p.damp = damp; p.ao = *out;
+    p.TPF = b->C * 24;
+    p.ea = exp(b->loss_a); p.eb = exp(b->loss_b); p.ec = exp(b->loss_c);
+    const int need = ENT_PAD + DDI_SZ + YS_SZ;
+    p.at_size = p.TPF * 9 > need ? p.TPF * 9 : need;
+    const size_t smem = (size_t)(b->C * CPE_CAM_STRIDE + A_AT + p.at_size) * sizeof(double);
+    int threads = ((p.TPF + 31) / 32) * 32;
+    if (threads < 160) threads = 160;               // >= 5 warps: one per elimination group
+    const dim3 grid(b->N, b->S, 1);
+    if (threads <= 160) return launch_asm<160, 5>(p, grid, threads, smem, (cudaStream_t)stream);
+    return launch_asm<192, 4>(p, grid, threads, smem, (cudaStream_t)stream);
+}

@@ -83,4 +83,37 @@ __device__ __forceinline__ void redescending(double E, double a, double b, doubl
            (sb - sc) * a * (c - E) / cb + dc * k4;
 }
 
+// R = Rz(psi) Ry(theta) Rx(phi) from sc = {sin phi, cos phi, sin theta, cos theta, sin psi, cos psi}
+// (reference shared/physical_education/utils.py:39-64, links.py:483)
+__device__ __forceinline__ void rot_from_sc(const double *sc, double *M) {
+    const double sf = sc[0], cf = sc[1], st = sc[2], ct = sc[3], sp = sc[4], cp = sc[5];
+    M[0] = cp * ct; M[1] = cp * st * sf - sp * cf; M[2] = cp * st * cf + sp * sf;
+    M[3] = sp * ct; M[4] = sp * st * sf + cp * cf; M[5] = sp * st * cf - cp * sf;
+    M[6] = -st;     M[7] = ct * sf;                M[8] = ct * cf;
+}
+
+// (dR/dangle_a) . v  for a = 0 (phi), 1 (theta), 2 (psi)
+__device__ __forceinline__ void drot_times(const double *sc, int a, double v0, double v1, double v2, double *o) {
+    const double sf = sc[0], cf = sc[1], st = sc[2], ct = sc[3], sp = sc[4], cp = sc[5];
+    if (a == 0) {
+        o[0] = (cp * st * cf + sp * sf) * v1 + (-cp * st * sf + sp * cf) * v2;
+        o[1] = (sp * st * cf - cp * sf) * v1 + (-sp * st * sf - cp * cf) * v2;
+        o[2] = (ct * cf) * v1 + (-ct * sf) * v2;
+    } else if (a == 1) {
+        o[0] = (-cp * st) * v0 + (cp * ct * sf) * v1 + (cp * ct * cf) * v2;
+        o[1] = (-sp * st) * v0 + (sp * ct * sf) * v1 + (sp * ct * cf) * v2;
+        o[2] = (-ct) * v0 + (-st * sf) * v1 + (-st * cf) * v2;
+    } else {
+        o[0] = (-sp * ct) * v0 + (-sp * st * sf - cp * cf) * v1 + (-sp * st * cf + cp * sf) * v2;
+        o[1] = (cp * ct) * v0 + (cp * st * sf - sp * cf) * v1 + (cp * st * cf + sp * sf) * v2;
+        o[2] = 0.0;
+    }
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    return v;
+}
+
 }  // namespace cpe

@@ -13,9 +13,9 @@ import torch
 from . import _lib, skeleton
 
 FISHEYE, PINHOLE = 0, 1
-_I32_KEYS = ("chain_link", "slot_of", "eq_pairs", "ineq_idx", "ind_idx", "ind_pos", "blk_nodes", "blk_id",
-             "blk_item_ptr", "blk_items", "blk_eq_ptr", "blk_eq_items", "grp_ndep", "grp_nnb", "grp_dep", "grp_nb",
-             "grp_nbpos", "u_off", "u_item")
+_I32_KEYS = ("chain_link", "eq_pairs", "ineq_idx", "ind_idx", "ind_pos", "grp_ndep", "grp_nnb", "grp_dep", "grp_nb",
+             "u_off", "u_item", "ent_pq", "a_ptr", "a_items", "e_ptr", "e_items", "i_ptr", "i_items", "diag_ent",
+             "grad_ent", "grp_src", "s_src", "s_ptr", "s_items")
 _F64_KEYS = ("ineq_bounds", "wq", "meas_w")
 
 
@@ -37,6 +37,7 @@ class Model:
         self.device = torch.device(device)
         self.kinetic_dataset = kinetic_dataset
         self.tables = skeleton.build_tables(kinetic_dataset)
+        self.tables.update(skeleton.assemble_tables(self.tables))
         self.t = {}
         for k in _I32_KEYS:
             self.t[k] = torch.as_tensor(np.ascontiguousarray(self.tables[k], dtype=np.int32), device=self.device)
@@ -45,9 +46,8 @@ class Model:
         self.n_ineq = int(self.tables["n_ineq"])
         self.n_groups = int(self.tables["n_groups"])
         s = _lib.CpeModel()
-        s.n_ineq, s.n_blocks = self.n_ineq, int(self.tables["n_blocks"])
-        s.n_groups, s.n_blk_items = self.n_groups, int(self.tables["n_blk_items"])
-        s.n_u = int(self.tables["n_u"])
+        s.n_ineq, s.n_groups = self.n_ineq, self.n_groups
+        s.n_u, s.n_ent = int(self.tables["n_u"]), int(self.tables["n_ent"])
         self.jac_width = 2 * (72 + s.n_u)
         for k in _I32_KEYS + _F64_KEYS:
             setattr(s, k, self.t[k].data_ptr())

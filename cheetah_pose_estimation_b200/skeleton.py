@@ -341,3 +341,117 @@ def pack_camera(K, D, R, t, mult=1.0):
     cam[17:20] = np.asarray(t, float).reshape(3)
     cam[20] = mult
     return cam
+
+
+# ---- gather tables of the fused normal-equation kernel (K2, csrc/cpe_assemble.cu) --------------------------------
+# Per-frame shared-memory vector spaces the tables index (offsets in doubles):
+#   G space: [0,9) the identity columns e_x,e_y,e_z (3 doubles each), then at 10 the chain-derivative blocks
+#            U = dR/dangle . v, 10 doubles per (marker, chain link): angle a at +3a          (same layout as K1)
+#   B space: [0,216) A_l columns (9 per marker), at 216 the blocks A_l U (same 10-double layout), at 876 b_l (3 per marker)
+G_U0, B_U0, B_G0, B_SIZE = 10, 216, 216 + 660, 216 + 660 + 72
+GRAD_Q = 63          # ent_pq low field of a gradient entry
+
+
+def _g_off(u_off, l, ci):
+    if ci < 3:
+        return 3 * ci
+    u = int(u_off[l]) + ci - 3
+    return G_U0 + 10 * (u // 3) + 3 * (u % 3)
+
+
+def _b_off(u_off, l, ci):
+    if ci < 3:
+        return 9 * l + 3 * ci
+    u = int(u_off[l]) + ci - 3
+    return B_U0 + 10 * (u // 3) + 3 * (u % 3)
+
+
+def assemble_tables(t=None, kinetic_dataset=False):
+    """Static gather lists for K2.  Entry e is either a lower-triangular Hessian entry (p >= q) of the tree-sparse
+    frame Hessian or (q = GRAD_Q) the gradient component p.  Its value is
+        sum_{A items} G[offG] . B[offB]   +   mu_eq * sum_{E items} eqg[i] * (eqg[j] | eqr)   +   mu_in * sum_{I items} +-(act | v)
+    Entries are ordered by decreasing cost so that a round-robin assignment to threads is balanced."""
+    if t is None:
+        t = build_tables(kinetic_dataset)
+    u_off, cols = t["u_off"], None
+    chain_link = t["chain_link"].reshape(N_MARKERS, MAX_CHAIN)
+    _, _, cols = jacobian_pattern(chain_link)
+    eq = t["eq_pairs"].reshape(-1, 4)
+    ineq = t["ineq_idx"].reshape(-1, 2)
+    A, E, I = {}, {}, {}
+    for l in range(N_MARKERS):
+        for ip, p in enumerate(cols[l]):
+            for iq, q in enumerate(cols[l]):
+                if p >= q:
+                    A.setdefault((p, q), []).append((_g_off(u_off, l, ip) << 16) | _b_off(u_off, l, iq))
+            A.setdefault((p, GRAD_Q), []).append((_g_off(u_off, l, ip) << 16) | (B_G0 + 3 * l))
+    for e, (la, lb, _, _) in enumerate(eq):
+        cc = [3 + 3 * la + a for a in range(3)] + [3 + 3 * lb + a for a in range(3)]
+        for i, p in enumerate(cc):
+            for j, q in enumerate(cc):
+                if p >= q:
+                    E.setdefault((p, q), []).append(((e * 6 + i) << 8) | (e * 6 + j))
+            E.setdefault((p, GRAD_Q), []).append(((e * 6 + i) << 8) | e)
+    for j, (ip, im) in enumerate(ineq):
+        ip, im = int(ip), int(im)
+        I.setdefault((ip, ip), []).append(j << 1)
+        I.setdefault((ip, GRAD_Q), []).append(j << 1)
+        if im >= 0:
+            I.setdefault((im, im), []).append(j << 1)
+            I.setdefault((max(ip, im), min(ip, im)), []).append((j << 1) | 1)
+            I.setdefault((im, GRAD_Q), []).append((j << 1) | 1)
+    keys = sorted(set(A) | set(E) | set(I))
+    cost = {k: 12 * len(A.get(k, [])) + 4 * len(E.get(k, [])) + 4 * len(I.get(k, [])) for k in keys}
+    keys.sort(key=lambda k: (-cost[k], k))
+    ent_of = {k: i for i, k in enumerate(keys)}
+    ent_pq = np.array([p * 64 + q for (p, q) in keys], np.int32)
+
+    def csr(d):
+        ptr, items = [0], []
+        for k in keys:
+            items += d.get(k, [])
+            ptr.append(len(items))
+        return np.array(ptr, np.int32), np.array(items if items else [0], np.int32)
+
+    a_ptr, a_items = csr(A)
+    e_ptr, e_items = csr(E)
+    i_ptr, i_items = csr(I)
+
+    def ent(p, q):
+        return ent_of.get((max(p, q), min(p, q)), -1)
+
+    diag_ent = np.array([ent(p, p) for p in range(54)], np.int32)
+    grad_ent = np.array([ent_of[(p, GRAD_Q)] for p in range(54)], np.int32)
+    G = int(t["n_groups"])
+    gdep, gnb = t["grp_dep"].reshape(G, GRP_MAX_DEP), t["grp_nb"].reshape(G, GRP_MAX_NB)
+    nd, nn = t["grp_ndep"], t["grp_nnb"]
+    # elimination tableau sources: [G][6][19] entry index, -1 = structural zero, -2 = identity (padding row)
+    grp_src = -np.ones((G, GRP_MAX_DEP, GRP_MAX_DEP + GRP_MAX_NB + 1), np.int32)
+    for g in range(G):
+        for i in range(GRP_MAX_DEP):
+            if i >= nd[g]:
+                grp_src[g, i, i] = -2
+                continue
+            for j in range(nd[g]):
+                grp_src[g, i, j] = ent(int(gdep[g, i]), int(gdep[g, j]))
+            for j in range(nn[g]):
+                grp_src[g, i, GRP_MAX_DEP + j] = ent(int(gdep[g, i]), int(gnb[g, j]))
+            grp_src[g, i, GRP_MAX_DEP + GRP_MAX_NB] = grad_ent[int(gdep[g, i])]
+    ind = t["ind_idx"]
+    s_src = np.array([[ent(int(ind[r]), int(ind[c])) for c in range(N_IND)] for r in range(N_IND)], np.int32)
+    nbpos = t["grp_nbpos"].reshape(G, N_IND)
+    s_ptr, s_items = [0], []
+    for r in range(N_IND):
+        for c in range(N_IND + 1):            # column 28 = the reduced gradient ghat[r]
+            for g in range(G):
+                a = int(nbpos[g, r])
+                if a < 0:
+                    continue
+                if c == N_IND:
+                    s_items.append((g << 8) | (a << 4) | 15)
+                elif nbpos[g, c] >= 0:
+                    s_items.append((g << 8) | (a << 4) | int(nbpos[g, c]))
+            s_ptr.append(len(s_items))
+    return dict(n_ent=len(keys), ent_pq=ent_pq, a_ptr=a_ptr, a_items=a_items, e_ptr=e_ptr, e_items=e_items,
+                i_ptr=i_ptr, i_items=i_items, diag_ent=diag_ent, grad_ent=grad_ent, grp_src=grp_src.reshape(-1),
+                s_src=s_src.reshape(-1), s_ptr=np.array(s_ptr, np.int32), s_items=np.array(s_items, np.int32))

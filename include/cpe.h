@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 101          /* 0.1.1 */
+#define CPE_VERSION 102          /* 0.1.2 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -62,13 +62,10 @@ extern "C" {
 /* Static skeleton tables (device pointers; built once on the host from the chain topology). */
 typedef struct cpe_model {
     int32_t n_ineq;                 /* two-sided linear inequality rows per frame (<= CPE_MAX_INEQ) */
-    int32_t n_blocks;               /* nonzero lower-triangular 3x3 node-pair blocks of the frame Hessian */
     int32_t n_groups;               /* elimination groups of dependent coordinates */
-    int32_t n_blk_items;
     int32_t n_u;                    /* packed chain columns over all markers: sum_l 3*chainlen(l) (198) */
-    int32_t reserved_;
+    int32_t n_ent;                  /* Hessian lower-triangle nonzeros + 54 gradient entries (639) */
     const int32_t *chain_link;      /* [24*5] link index or -1 */
-    const int32_t *slot_of;         /* [24*18] slot (0 = xyz, 1..5 = chain position) of node in marker chain, or -1 */
     const int32_t *eq_pairs;        /* [26*4] link_a, link_b, axis_a, axis_b : (R_a e_axa).(R_b e_axb) = 0 */
     const int32_t *ineq_idx;        /* [n_ineq*2] coord_plus, coord_minus (-1 = none): lo <= q[+] - q[-] <= up */
     const double *ineq_bounds;      /* [n_ineq*2] lo, up */
@@ -76,19 +73,26 @@ typedef struct cpe_model {
     const double *meas_w;           /* [3*24] 1/R_pw[w][l]  (acinoset_misc.py:231) */
     const int32_t *ind_idx;         /* [28] coordinates with wq != 0 */
     const int32_t *ind_pos;         /* [54] position of coord in ind_idx or -1 */
-    const int32_t *blk_nodes;       /* [n_blocks*2] row node >= col node */
-    const int32_t *blk_id;          /* [18*18] block id of (row node, col node) for row >= col, else -1 */
-    const int32_t *blk_item_ptr;    /* [n_blocks+1] */
-    const int32_t *blk_items;       /* marker indices whose chain contains the block's row node */
-    const int32_t *blk_eq_ptr;      /* [n_blocks+1] */
-    const int32_t *blk_eq_items;    /* eq index*4 + (row side)*2 + (col side); side 0 = link_a, 1 = link_b */
     const int32_t *grp_ndep;        /* [n_groups] */
     const int32_t *grp_nnb;         /* [n_groups] */
     const int32_t *grp_dep;         /* [n_groups*6] coordinate indices */
     const int32_t *grp_nb;          /* [n_groups*12] coordinate indices (independent) */
-    const int32_t *grp_nbpos;       /* [n_groups*28] position of ind coord r in the group's nb list, or -1 */
     const int32_t *u_off;           /* [25] first packed chain column of marker l (prefix sum of 3*chainlen) */
     const int32_t *u_item;          /* [n_u] (marker << 8) | (chain slot << 4) | angle, per packed chain column */
+    /* static gather lists of K2 (skeleton.assemble_tables); entry e = Hessian nonzero (p >= q) or gradient p */
+    const int32_t *ent_pq;          /* [n_ent] p*64 + q ; q = 63 marks a gradient entry */
+    const int32_t *a_ptr;           /* [n_ent+1] marker items: (offset in G space << 16) | offset in B space */
+    const int32_t *a_items;
+    const int32_t *e_ptr;           /* [n_ent+1] joint-equality items: (eqg index << 8) | (eqg index | eq row) */
+    const int32_t *e_items;
+    const int32_t *i_ptr;           /* [n_ent+1] inequality items: (row << 1) | negative */
+    const int32_t *i_items;
+    const int32_t *diag_ent;        /* [54] entry of H(p,p) */
+    const int32_t *grad_ent;        /* [54] entry of g(p) */
+    const int32_t *grp_src;         /* [n_groups*6*19] tableau sources: entry, -1 = zero, -2 = identity padding */
+    const int32_t *s_src;           /* [28*28] entry of H(ind_r, ind_c) or -1 */
+    const int32_t *s_ptr;           /* [28*29+1] Schur items of S(r,c) (c = 28: ghat): (group << 8) | (a << 4) | b */
+    const int32_t *s_items;
 } cpe_model;
 
 /* One batch of sequences. */
