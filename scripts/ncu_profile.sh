@@ -3,10 +3,10 @@
 set -x
 TAG=${1:-rX}
 CMD="python bench.py --seqs 64 --wave 32 --lm-seqs 16 --lm-iters 4 --cpu-seqs 0 --steps 2 --warmup 1 --no-e2e"
-K="eval_kernel|frame_kernel|band_solve|step_apply|reduce_cost|step_accept|update_multipliers"
+K="eval_kernel|assemble_kernel|band_solve|step_apply|reduce_cost|step_accept|update_multipliers"
 $CMD > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"$K" -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/ncu1.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:"eval_kernel" -s 1 -c 2 -o gpurun_out/${TAG}_evaljac $CMD > gpurun_out/ncu2.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:"frame_kernel" -c 1 -o gpurun_out/${TAG}_assemble $CMD > gpurun_out/ncu3.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:"assemble_kernel" -c 1 -o gpurun_out/${TAG}_assemble $CMD > gpurun_out/ncu3.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:"band_solve" -c 1 -o gpurun_out/${TAG}_bandsolve $CMD > gpurun_out/ncu4.log 2>&1
 cp cheetah_pose_estimation_b200/libcpe_b200.so gpurun_out/${TAG}_libcpe_b200.so; ls -la gpurun_out

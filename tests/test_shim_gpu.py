@@ -1,0 +1,56 @@
+"""End-to-end drop-in test on real clips: init_trajectory -> estimate_kinematics -> save through the mirrored API,
+from an AcinoSet-style directory rebuilt out of the reference's shipped outputs (cameras / detections recovered,
+SURVEY.md G8).  The DLC likelihood mask of the original run is lost, so optimiser parity against IPOPT is UNPINNED:
+the checks are (i) file format and keys equal the shipped fte.pickle, (ii) our optimum costs no more than the shipped
+trajectory under the SAME (all-on) objective, (iii) it stays within centimetres of the shipped 3D trajectory."""
+import os
+import pickle
+
+import numpy as np
+import pytest
+
+from tests._dataset import build_clip_dir
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("animal,fname,path", [("jules", "clip_jules_run1_1.npz", "2017_08_29/top/jules/run1_1"),
+                                               ("phantom", "clip_phantom_run.npz", "2019_03_07/phantom/run")])
+def test_kinematic_reconstruction_of_a_real_clip(golden_dir, tmp_path, animal, fname, path):
+    import torch
+    from cheetah_pose_estimation_b200 import acinoset_misc as misc, acinoset_opt as opt, engine, skeleton as sk
+    g = np.load(os.path.join(golden_dir, fname))
+    ref = np.load(os.path.join(golden_dir, "save_ref.npz"))
+    root = str(tmp_path)
+    build_clip_dir(root, path, g)
+    est = opt.init_trajectory(root, path, animal, kinetic_dataset=False, solver_path="ignored", kinematic_model=True)
+    assert est.meas.shape == g["detections"].shape[:2] + (24, 1, 4)
+    ok = opt.estimate_kinematics(est, solver_output=True)
+    assert ok
+    out_dir = os.path.join(root, path, "fte_kinematic")
+    d = pickle.load(open(os.path.join(out_dir, "fte.pickle"), "rb"))
+    assert sorted(d.keys()) == list(ref[f"{animal}_keys"])
+    N, C = g["detections"].shape[:2]
+    assert d["q"].shape == (N, 54) and d["x"].shape == (N, 28) and d["positions"].shape == (N, 24, 3)
+    assert d["meas_err"].shape == (N, C, 24, 2, 1) and d["com_vel"].shape == (N - 1, 3)
+    assert d["start_frame"] == int(g["start_frame"]) and d["processing_time_s"] > 0
+    for c in range(C):
+        assert os.path.exists(os.path.join(out_dir, f"cam{c + 1}_fte.csv"))
+    # implicit-Euler relations of the saved derivatives
+    h = 1.0 / float(g["fps"])
+    assert np.abs(d["q"][1:] - d["q"][:-1] - h * d["dq"][1:]).max() < 1e-12
+    assert np.abs(d["dq"][1:] - d["dq"][:-1] - h * d["ddq"][1:]).max() < 1e-9
+    # (ii) same objective evaluated at the shipped optimum
+    _, cvec = sk.marker_chains(est.lengths, est.radii)
+    batch = engine.Batch.from_numpy(est.meas[None], est.packed_cameras()[None], cvec[None], [h])
+    sv = engine.Solver(est.model, batch, with_solver=False)
+    c_ship = sv.evaluate(torch.as_tensor(g["q"][None].copy(), device="cuda"))["cost"][0].cpu().numpy()
+    obj_ship = 1e-3 * (c_ship[0] + c_ship[1])
+    assert d["obj_cost"] <= obj_ship * 1.005, (d["obj_cost"], obj_ship)
+    # (iii) distance to the shipped trajectory (different likelihood mask => not identical)
+    mpjpe = misc.traj_error(d["positions"].copy(), g["positions"].copy(), centered=True).mean()
+    mpe = misc.traj_error(d["positions"].copy(), g["positions"].copy()).mean()
+    print(f"{path}: obj {d['obj_cost']:.3f} (shipped trajectory under the same objective {obj_ship:.3f}; shipped "
+          f"obj_cost {float(g['obj_cost']):.3f} with the lost mask), MPJPE {mpjpe:.1f} mm, MPE {mpe:.1f} mm, "
+          f"{d['processing_time_s']:.3f} s vs IPOPT {float(g['processing_time_s']):.1f} s")
+    assert mpjpe < 30.0 and mpe < 60.0
