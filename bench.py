@@ -31,6 +31,7 @@ UNIT = "frame.views/s"
 # detections 24 x (u,v,w) f32 = 288 B, state 54 x 8 B / C=6 = 72 B, residuals 48 x 8 B = 384 B,
 # chain-sparse Jacobian 540 nnz x 8 B = 4320 B.
 ALGO_BYTES_PER_FV = 288 + 72 + 384 + 4320
+TRAFFIC_KEY = "eval_kernel_jac"
 
 
 def parse_args():
@@ -366,8 +367,11 @@ def main():
         achieved = fv_launch * ALGO_BYTES_PER_FV / (kern_ms * 1e-3) / 1e9
         traffic = None
         try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("eval_kernel_jac")
-        except (OSError, ValueError):
+            # DRAM bytes per frame.view of the kernel from the committed `ncu --set full` capture, scaled to this
+            # launch size (bytes per launch, like `achieved`)
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[TRAFFIC_KEY]
+            traffic = tj["dram_bytes_per_frame_view"] * fv_launch
+        except (OSError, ValueError, KeyError):
             pass
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
                 "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
