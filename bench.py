@@ -31,6 +31,8 @@ UNIT = "frame.views/s"
 # detections 24 x (u,v,w) f32 = 288 B, state 54 x 8 B / C=6 = 72 B, residuals 48 x 8 B = 384 B,
 # chain-sparse Jacobian 540 nnz x 8 B = 4320 B.
 ALGO_BYTES_PER_FV = 288 + 72 + 384 + 4320
+# FP32 flavour (cpe_eval_f32): residuals 48 x 4 B, Jacobian 540 x 4 B (SURVEY.md 8d mode A = 2712 B)
+ALGO_BYTES_PER_FV_F32 = 288 + 72 + 192 + 2160
 TRAFFIC_KEY = "eval_kernel_jac"
 
 
@@ -48,6 +50,7 @@ def parse_args():
     ap.add_argument("--lm-iters", type=int, default=20)
     ap.add_argument("--cpu-seqs", type=int, default=64, help="sequences of the cpu_baseline sample (0 = skip)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-f32", action="store_true", help="skip the FP32-flavour leg")
     ap.add_argument("--seed", type=int, default=0)
     return ap.parse_args()
 
@@ -208,7 +211,8 @@ def run_b200(a):
     S, N, C = a.seqs, a.frames, a.cams
     wave = min(a.wave, S)
     model = engine.Model(dev)
-    batch, q_true, q_init = synthetic.make_device_problem(S, N, C, seed=a.seed + 1000 * rank, device=dev)
+    batch, q_true, q_init = synthetic.make_device_problem(S, N, C, seed=a.seed + 1000 * rank, device=dev,
+                                                          dlc_native=True)
     gen = torch.Generator(device=dev)
     gen.manual_seed(a.seed + 100 + rank)
     q = (q_true + 0.05 * torch.randn(q_true.shape, generator=gen, device=dev, dtype=torch.float64)).contiguous()
@@ -253,6 +257,36 @@ def run_b200(a):
     launches = 2 * len(waves) * a.steps
     cost_sum = cost_all.sum(dim=0)
 
+    # ---- the scaled FP32 flavour of the same step (cpe_eval_f32): reported beside the FP64 headline ------------------
+    f32 = None
+    if not a.no_f32:
+        f32b = {"jac": torch.empty(wave, N, C, model.jac_width, dtype=torch.float32, device=dev),
+                "resid": torch.empty(wave, N, C, 24, 1, 2, dtype=torch.float32, device=dev)}
+        waves32 = [(sv, qw, {"jac": f32b["jac"][:qw.shape[0]], "resid": f32b["resid"][:qw.shape[0]]}) for sv, qw, _ in waves]
+        cost32 = torch.zeros(S, 4, **f64)
+        pairs32 = []
+
+        def step32(record=False):
+            for i, (sv, qw, bw) in enumerate(waves32):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                sv.evaluate_launch(qw, bw, cost32[i * wave:i * wave + qw.shape[0]], record_mid=e1)
+                if record:
+                    pairs32.append((e0, e1))
+        for _ in range(a.warmup):
+            step32()
+        barrier()
+        u0, u1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        u0.record()
+        for _ in range(a.steps):
+            step32(record=True)
+        u1.record()
+        barrier()
+        rel = float(((cost32.sum(dim=0)[0] - cost_sum[0]) / cost_sum[0]).abs())
+        f32 = dict(ms=u0.elapsed_time(u1), kern_ms=sum(x.elapsed_time(y) for x, y in pairs32) / len(pairs32),
+                   rel_cost_diff=rel)
+        del f32b, waves32
+
     # ---- end to end through the public host-buffer API ----------------------------------------------------------
     e2e = None
     if not a.no_e2e:
@@ -279,7 +313,7 @@ def run_b200(a):
         del hev, h_q, h_meas
         torch.cuda.empty_cache()
     clk = clocks.stop() if rank == 0 else None
-    return dict(rank=rank, world=world, dev=dev, model=model, batch=batch, q=q, q_init=q_init, ms=ms, kern_ms=kern_ms,
+    return dict(rank=rank, world=world, dev=dev, model=model, batch=batch, q=q, q_init=q_init, ms=ms, kern_ms=kern_ms, f32=f32,
                 n_kern=n_kern, launches=launches, e2e=e2e, clk=clk, cost_sum=cost_sum, wave=wave, barrier=barrier)
 
 
@@ -345,6 +379,8 @@ def main():
     ms = sharding.reduce_max(r["ms"], r["dev"])
     e2e_ms = sharding.reduce_max(r["e2e"][0] if r["e2e"] else 0.0, r["dev"])
     kern_ms = sharding.reduce_max(r["kern_ms"] / max(1, r["n_kern"]), r["dev"])
+    f32_ms = sharding.reduce_max(r["f32"]["ms"], r["dev"]) if r["f32"] else 0.0
+    f32_kern = sharding.reduce_max(r["f32"]["kern_ms"], r["dev"]) if r["f32"] else 0.0
     stats = torch.cat([r["cost_sum"], torch.tensor([float(r["launches"])], dtype=torch.float64, device=r["dev"])])
     if world > 1:
         dist.all_reduce(stats, op=dist.ReduceOp.SUM)
@@ -380,7 +416,7 @@ def main():
                            "l2": "inputs+outputs per launch (>= 20 GB) exceed the 126 MB L2; no flush needed",
                            "sharding": f"sequences, {a.seqs}/rank, no data-path collective"},
                 "gpu_launches": int(stats[4].item()),
-                "kernel": {"name": "eval_kernel<JAC>", "avg_ms": kern_ms, "frame_views_per_launch": fv_launch},
+                "kernel": {"name": "eval_kernel<double,JAC>", "avg_ms": kern_ms, "frame_views_per_launch": fv_launch},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                              "frac": achieved / peak, "traffic": traffic,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650",
@@ -389,7 +425,15 @@ def main():
         if r["e2e"]:
             line["e2e"] = {"value": fv_total * a.steps / (e2e_ms * 1e-3), "unit": UNIT,
                            "h2d_bytes_per_step": r["e2e"][1], "d2h_bytes_per_step": r["e2e"][2],
-                           "api": "engine.HostEvaluator -> cpe_eval_host_f64 (pinned host q + detections in, cost out)"}
+                           "api": "engine.HostEvaluator -> cpe_eval_host_f64 (pinned host q + DLC-native (x,y,likelihood) float3 detections in, cost out)"}
+        if r["f32"]:
+            ach32 = fv_launch * ALGO_BYTES_PER_FV_F32 / (f32_kern * 1e-3) / 1e9
+            line["f32"] = {"value": fv_total * a.steps / (f32_ms * 1e-3), "unit": UNIT, "ms_per_step": f32_ms / a.steps,
+                           "kernel": {"name": "eval_kernel<float,JAC>", "avg_ms": f32_kern},
+                           "roofline": {"bound": "hbm", "achieved": ach32, "peak": peak, "unit": "GB/s",
+                                        "frac": ach32 / peak, "algorithmic_bytes_per_frame_view": ALGO_BYTES_PER_FV_F32},
+                           "rel_diff_of_measurement_cost_vs_f64": r["f32"]["rel_cost_diff"],
+                           "api": "cpe_eval_f32 (scaled FP32 residual path; residuals/Jacobian in float, FK and cost sums FP64)"}
         if lm is not None:
             line["lm"] = lm
         if world == 1:

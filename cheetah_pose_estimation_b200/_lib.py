@@ -29,7 +29,7 @@ class CpeModel(C.Structure):
 class CpeBatch(C.Structure):
     _fields_ = [
         ("S", C.c_int32), ("N", C.c_int32), ("C", C.c_int32), ("W", C.c_int32),
-        ("cam_model", C.c_int32), ("meas_is_f64", C.c_int32),
+        ("cam_model", C.c_int32), ("meas_layout", C.c_int32), ("dlc_thresh", C.c_double),
         ("mu_eq", C.c_double), ("mu_in", C.c_double),
         ("loss_a", C.c_double), ("loss_b", C.c_double), ("loss_c", C.c_double),
         ("n_frames", c_i32p), ("h", c_f64p), ("meas", C.c_void_p), ("cams", c_f64p), ("chain_vec", c_f64p),
@@ -40,6 +40,11 @@ class CpeBatch(C.Structure):
 class CpeEvalOut(C.Structure):
     _fields_ = [("frame_cost", c_f64p), ("pose", c_f64p), ("resid", c_f64p), ("c_eq", c_f64p), ("v_in", c_f64p),
                 ("jac", c_f64p)]
+
+
+class CpeEvalOutF32(C.Structure):
+    _fields_ = [("frame_cost", c_f64p), ("pose", c_f64p), ("resid", C.c_void_p), ("c_eq", c_f64p), ("v_in", c_f64p),
+                ("jac", C.c_void_p)]
 
 
 class CpeAssembleOut(C.Structure):
@@ -54,6 +59,7 @@ class CpeSolveIO(C.Structure):
 EXPORTS = {
     "cpe_version": (C.c_int, []),
     "cpe_eval_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpeBatch), c_f64p, C.POINTER(CpeEvalOut), C.c_void_p]),
+    "cpe_eval_f32": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpeBatch), c_f64p, C.POINTER(CpeEvalOutF32), C.c_void_p]),
     "cpe_reduce_cost_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, C.c_void_p]),
     "cpe_assemble_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpeBatch), c_f64p, c_f64p,
                                    C.POINTER(CpeAssembleOut), C.c_void_p]),

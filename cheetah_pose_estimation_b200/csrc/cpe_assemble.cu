@@ -68,13 +68,9 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
     const bool mvalid = tid < TPF;
     const int mc = tid / 24, ml = tid - mc * 24;
     const size_t midx0 = ((fidx * C + mc) * 24 + ml) * W;
-    float4 m4 = make_float4(0.f, 0.f, 0.f, 0.f);
-    double4 m8 = make_double4(0.0, 0.0, 0.0, 0.0);
-    const bool m64 = p.b.meas_is_f64 != 0;
-    if (mvalid) {
-        if (m64) m8 = reinterpret_cast<const double4 *>(p.b.meas)[midx0];
-        else m4 = __ldg(reinterpret_cast<const float4 *>(p.b.meas) + midx0);
-    }
+    MeasRaw mraw;
+    mraw.d = make_double4(0.0, 0.0, 0.0, 0.0);
+    if (mvalid) meas_fetch(p.b, midx0, mraw);
     const double *qf = p.q + fidx * 54;
     for (int c = tid; c < 54; c += nt) fr[A_QO + c] = qf[c];
     for (int i = tid; i < C * CPE_CAM_STRIDE; i += nt) cam[i] = p.b.cams[(size_t)s * C * CPE_CAM_STRIDE + i];
@@ -189,12 +185,8 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
         double hu = 0.0, hv = 0.0, gu = 0.0, gv = 0.0;
         for (int w = 0; w < W; ++w) {
             double um, vm, gate;
-            if (w > 0) {
-                if (m64) m8 = reinterpret_cast<const double4 *>(p.b.meas)[midx0 + w];
-                else m4 = __ldg(reinterpret_cast<const float4 *>(p.b.meas) + midx0 + w);
-            }
-            if (m64) { um = m8.x; vm = m8.y; gate = m8.z; }
-            else { um = (double)m4.x; vm = (double)m4.y; gate = (double)m4.z; }
+            if (w > 0) meas_fetch(p.b, midx0 + w, mraw);
+            meas_unpack(p.b, mraw, um, vm, gate);
             const double wgt = gate * p.m.meas_w[w * 24 + ml] * cmult;
             const double eu = wgt * (pr.u - um), ev = wgt * (pr.v - vm);
             const double Eu = fabs(eu), Ev = fabs(ev);

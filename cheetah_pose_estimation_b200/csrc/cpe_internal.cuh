@@ -66,6 +66,121 @@ __device__ __forceinline__ void project_point(const double *X, const double *cam
     }
 }
 
+// ---- detections in the three accepted layouts (cpe_batch.meas_layout) -----------------------------------------------
+// Raw registers of one detection: fetched early (before the FK phases), unpacked where it is used.
+union MeasRaw {
+    float4 f;
+    double4 d;
+};
+
+__device__ __forceinline__ void meas_fetch(const cpe_batch &b, size_t idx, MeasRaw &m) {
+    if (b.meas_layout == CPE_MEAS_F64X4) {
+        m.d = reinterpret_cast<const double4 *>(b.meas)[idx];
+    } else if (b.meas_layout == CPE_MEAS_F32X4) {
+        m.f = __ldg(reinterpret_cast<const float4 *>(b.meas) + idx);
+    } else {                                   // CPE_MEAS_F32X3: DLC-native (x, y, likelihood)
+        const float *f = reinterpret_cast<const float *>(b.meas) + 3 * idx;
+        m.f.x = __ldg(f); m.f.y = __ldg(f + 1); m.f.z = __ldg(f + 2);
+    }
+}
+
+// (u, v, gate); for the DLC-native layout the gate is the reference's strict test likelihood > dlc_thresh
+// (acinoset_misc.py:231).
+__device__ __forceinline__ void meas_unpack(const cpe_batch &b, const MeasRaw &m, double &u, double &v, double &gate) {
+    if (b.meas_layout == CPE_MEAS_F64X4) {
+        u = m.d.x; v = m.d.y; gate = m.d.z;
+    } else {
+        u = (double)m.f.x; v = (double)m.f.y;
+        gate = b.meas_layout == CPE_MEAS_F32X4 ? (double)m.f.z : ((double)m.f.z > b.dlc_thresh ? 1.0 : 0.0);
+    }
+}
+
+// ---- projection from CAMERA-frame coordinates, templated on the scalar type (K1) --------------------------------------
+// cam (type T) = fx fy cx cy D0..D3 R[9] ...; returns pu = fx a s, pv = fy b s (principal point NOT added: the caller
+// folds cx - u_meas in FP64) and d(pu,pv)/d(world point) through R.
+template <typename T>
+struct ProjT {
+    T pu, pv;
+    T du[3], dv[3];
+};
+
+__device__ __forceinline__ double r_sqrt(double x) { return sqrt(x); }
+__device__ __forceinline__ float r_sqrt(float x) { return sqrtf(x); }
+__device__ __forceinline__ double r_atan(double x) { return atan(x); }
+__device__ __forceinline__ float r_atan(float x) { return atanf(x); }
+
+template <typename T, bool DERIV>
+__device__ __forceinline__ void project_cam(T x, T y, T z, const T *cam, int model, ProjT<T> &o) {
+    const T *R = cam + 8;
+    const T one = T(1);
+    T iz, s, g = T(0), a, b;
+    if (model == CPE_CAM_FISHEYE) {
+        iz = one / z;
+        a = x * iz; b = y * iz;
+        const T r2 = a * a + b * b;
+        const T r = r_sqrt(r2);
+        const T th = r_atan(r);
+        const T t2 = th * th;
+        const T poly = one + t2 * (cam[4] + t2 * (cam[5] + t2 * (cam[6] + t2 * cam[7])));
+        const T thd = th * poly;
+        const T re = r + T(1e-12);
+        if (DERIV) {
+            const T rr = r > T(0) ? r : one;
+            const T p1 = re * (one + r2);
+            const T inv = one / (p1 * rr);
+            const T ire = inv * (one + r2) * rr, i1r2 = inv * re * rr, ir = inv * p1;
+            s = thd * ire;
+            const T dpoly = one + t2 * (T(3) * cam[4] + t2 * (T(5) * cam[5] + t2 * (T(7) * cam[6] + t2 * T(9) * cam[7])));
+            const T ds_dr = (dpoly * i1r2 * re - thd) * (ire * ire);
+            g = r > T(0) ? ds_dr * ir : T(0);
+        } else {
+            s = thd / re;
+        }
+    } else {
+        iz = one / z;
+        a = x * iz; b = y * iz;
+        const T r2 = a * a + b * b;
+        s = one + r2 * (cam[4] + r2 * (cam[5] + r2 * cam[6]));
+        if (DERIV) g = T(2) * cam[4] + r2 * (T(4) * cam[5] + T(6) * r2 * cam[6]);
+    }
+    o.pu = cam[0] * (a * s);
+    o.pv = cam[1] * (b * s);
+    if (DERIV) {
+        const T xa = s + a * a * g, xb = a * b * g, yb = s + b * b * g;
+        const T ux = cam[0] * xa * iz, uy = cam[0] * xb * iz, uz = -cam[0] * (xa * a + xb * b) * iz;
+        const T vx = cam[1] * xb * iz, vy = cam[1] * yb * iz, vz = -cam[1] * (xb * a + yb * b) * iz;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            o.du[j] = ux * R[j] + uy * R[3 + j] + uz * R[6 + j];
+            o.dv[j] = vx * R[j] + vy * R[3 + j] + vz * R[6 + j];
+        }
+    }
+}
+
+// all three angle derivatives (dR/dphi, dR/dtheta, dR/dpsi) . v of one link: o[0..8] = {phi xyz, theta xyz, psi xyz}
+template <typename T>
+__device__ __forceinline__ void drot_all(const T *sc, T v0, T v1, T v2, T *o) {
+    const T sf = sc[0], cf = sc[1], st = sc[2], ct = sc[3], sp = sc[4], cp = sc[5];
+    const T stsf = st * sf, stcf = st * cf;
+    const T m01 = cp * stsf - sp * cf, m02 = cp * stcf + sp * sf;      // R[0][1], R[0][2]
+    const T m11 = sp * stsf + cp * cf, m12 = sp * stcf - cp * sf;      // R[1][1], R[1][2]
+    // d/dphi: columns rotate (col1 -> col2, col2 -> -col1)
+    o[0] = m02 * v1 - m01 * v2;
+    o[1] = m12 * v1 - m11 * v2;
+    o[2] = (ct * cf) * v1 - (ct * sf) * v2;
+    // d/dtheta
+    const T w = -st * v0 + ct * (sf * v1 + cf * v2);
+    o[3] = cp * w;
+    o[4] = sp * w;
+    o[5] = -ct * v0 - st * (sf * v1 + cf * v2);
+    // d/dpsi: rows rotate (row0 -> -row1, row1 -> row0)
+    const T x0 = cp * ct * v0 + m01 * v1 + m02 * v2;                   // (R v)[0]
+    const T x1 = sp * ct * v0 + m11 * v1 + m12 * v2;                   // (R v)[1]
+    o[6] = -x1;
+    o[7] = x0;
+    o[8] = T(0);
+}
+
 // Redescending loss of the reference (acinoset_misc.py:2001-2015) at magnitude E = |err| and its derivative
 // d rho / dE.  sigma(E - s) = 1 / (1 + exp(s) exp(-E)) needs a single exp per residual.
 __device__ __forceinline__ void redescending(double E, double a, double b, double c, double ea, double eb, double ec,

@@ -196,7 +196,8 @@ extern "C" int cpe_eval_host_f64(const cpe_model *model, const cpe_batch *bd, co
     if (!out_dev->frame_cost) return CPE_E_NULL;
     cudaStream_t st = (cudaStream_t)stream;
     const size_t frames = (size_t)bd->S * bd->N;
-    const size_t mbytes = frames * bd->C * 24 * bd->W * 4 * (bd->meas_is_f64 ? 8 : 4);
+    const size_t rec = bd->meas_layout == CPE_MEAS_F64X4 ? 32 : (bd->meas_layout == CPE_MEAS_F32X3 ? 12 : 16);
+    const size_t mbytes = frames * bd->C * 24 * bd->W * rec;
     cudaError_t e = cudaMemcpyAsync(d_q, h_q, frames * 54 * sizeof(double), cudaMemcpyHostToDevice, st);
     if (e != cudaSuccess) return (int)e;
     e = cudaMemcpyAsync(d_meas, h_meas, mbytes, cudaMemcpyHostToDevice, st);

@@ -13,6 +13,7 @@ import torch
 from . import _lib, skeleton
 
 FISHEYE, PINHOLE = 0, 1
+MEAS_F32X4, MEAS_F64X4, MEAS_F32X3 = 0, 1, 2      # include/cpe.h CPE_MEAS_*
 _I32_KEYS = ("chain_link", "eq_pairs", "ineq_idx", "ind_idx", "ind_pos", "grp_ndep", "grp_nnb", "grp_dep", "grp_nb",
              "u_off", "u_item", "ent_pq", "a_ptr", "a_items", "e_ptr", "e_items", "i_ptr", "i_items", "diag_ent",
              "grad_ent", "grp_src", "s_src", "s_ptr", "s_items")
@@ -59,7 +60,8 @@ class Batch:
     """Device-resident inputs of S sequences (`cpe_batch`)."""
     n_frames: torch.Tensor       # [S] int32
     h: torch.Tensor              # [S] f64
-    meas: torch.Tensor           # [S,N,C,24,W,4] f32 (or f64): u, v, gate, unused
+    meas: torch.Tensor           # [S,N,C,24,W,4] f32 (or f64): u, v, gate, unused -- or [S,N,C,24,W,3] f32:
+                                 # DLC-native x, y, likelihood (gated on the device by likelihood > dlc_thresh)
     cams: torch.Tensor           # [S,C,24] f64
     chain_vec: torch.Tensor      # [S,24,5,3] f64
     cam_model: int = FISHEYE
@@ -68,6 +70,13 @@ class Batch:
     mu_eq: float = 1e4
     mu_in: float = 1e4
     loss: tuple = (3.0, 10.0, 20.0)
+    dlc_thresh: float = 0.5
+
+    @property
+    def meas_layout(self):
+        if self.meas.shape[5] == 3:
+            return MEAS_F32X3
+        return MEAS_F64X4 if self.meas.dtype == torch.float64 else MEAS_F32X4
 
     @property
     def S(self):
@@ -89,13 +98,15 @@ class Batch:
         for t in (self.n_frames, self.h, self.meas, self.cams, self.chain_vec):
             assert t.is_cuda and t.is_contiguous()
         assert self.n_frames.dtype == torch.int32 and self.h.dtype == torch.float64
-        assert self.meas.dtype in (torch.float32, torch.float64) and self.meas.shape[3] == 24 and self.meas.shape[5] == 4
+        assert self.meas.dtype in (torch.float32, torch.float64) and self.meas.shape[3] == 24
+        assert self.meas.shape[5] == 4 or (self.meas.shape[5] == 3 and self.meas.dtype == torch.float32)
         assert self.cams.shape == (self.S, self.C, skeleton.CAM_STRIDE) and self.cams.dtype == torch.float64
         assert self.chain_vec.shape == (self.S, 24, 5, 3) and self.chain_vec.dtype == torch.float64
         b = _lib.CpeBatch()
         b.S, b.N, b.C, b.W = self.S, self.N, self.C, self.W
         b.cam_model = int(self.cam_model)
-        b.meas_is_f64 = 1 if self.meas.dtype == torch.float64 else 0
+        b.meas_layout = self.meas_layout
+        b.dlc_thresh = float(self.dlc_thresh)
         b.mu_eq, b.mu_in = float(self.mu_eq), float(self.mu_in)
         b.loss_a, b.loss_b, b.loss_c = self.loss
         b.n_frames, b.h = self.n_frames.data_ptr(), self.h.data_ptr()
@@ -110,14 +121,19 @@ class Batch:
                      chain_vec=self.chain_vec[s0:s1], cam_model=self.cam_model,
                      lam_eq=None if self.lam_eq is None else self.lam_eq[s0:s1],
                      lam_in=None if self.lam_in is None else self.lam_in[s0:s1],
-                     mu_eq=self.mu_eq, mu_in=self.mu_in, loss=self.loss)
+                     mu_eq=self.mu_eq, mu_in=self.mu_in, loss=self.loss, dlc_thresh=self.dlc_thresh)
 
     @staticmethod
-    def from_numpy(meas, cams, chain_vec, h, n_frames=None, device="cuda", cam_model=FISHEYE, meas_dtype=torch.float32):
-        """meas[S,N,C,24,W,3|4] (u, v, gate), cams[S,C,24], chain_vec[S,24,5,3], h[S]."""
+    def from_numpy(meas, cams, chain_vec, h, n_frames=None, device="cuda", cam_model=FISHEYE, meas_dtype=torch.float32,
+                   dlc_native=False, dlc_thresh=0.5):
+        """meas[S,N,C,24,W,3|4] (u, v, gate), cams[S,C,24], chain_vec[S,24,5,3], h[S].  With dlc_native=True the
+        last axis is the DLC triple (x, y, likelihood) and is kept as float3 records (gated on the device)."""
         meas = np.asarray(meas)
         S, N = meas.shape[:2]
-        if meas.shape[-1] == 3:
+        if dlc_native:
+            assert meas.shape[-1] == 3
+            meas_dtype = torch.float32
+        elif meas.shape[-1] == 3:
             meas = np.concatenate([meas, np.zeros(meas.shape[:-1] + (1,), meas.dtype)], -1)
         if n_frames is None:
             n_frames = np.full(S, N)
@@ -128,7 +144,7 @@ class Batch:
             meas=torch.as_tensor(np.ascontiguousarray(meas), device=dev).to(meas_dtype).contiguous(),
             cams=torch.as_tensor(np.ascontiguousarray(cams, dtype=np.float64), device=dev),
             chain_vec=torch.as_tensor(np.ascontiguousarray(chain_vec, dtype=np.float64), device=dev),
-            cam_model=cam_model)
+            cam_model=cam_model, dlc_thresh=dlc_thresh)
 
 
 class Solver:
@@ -164,32 +180,37 @@ class Solver:
             self.v_in = torch.zeros(S, N, model.n_ineq, **f64)
 
     # ---- K1 --------------------------------------------------------------------------------------------------
-    def evaluate(self, q, pose=False, resid=False, constraints=False, jac=False, cost_out=None, buffers=None):
+    def evaluate(self, q, pose=False, resid=False, constraints=False, jac=False, cost_out=None, buffers=None, f32=False):
         """cost[S,4] = (measurement, model, al_eq, al_in) and optional per-frame outputs.  `buffers` may hold
-        preallocated output tensors ("pose", "resid", "jac") to write into instead of allocating."""
+        preallocated output tensors ("pose", "resid", "jac") to write into instead of allocating.  f32=True runs the
+        scaled FP32 flavour (cpe_eval_f32): resid / jac come back as float32."""
         b = self.b
         assert q.is_cuda and q.dtype == torch.float64 and q.is_contiguous() and q.shape == (b.S, b.N, 54)
         out = {}
         buffers = buffers or {}
-        eo = _lib.CpeEvalOut()
+        eo = _lib.CpeEvalOutF32() if f32 else _lib.CpeEvalOut()
         eo.frame_cost = self.frame_cost.data_ptr()
         f64 = dict(dtype=torch.float64, device=q.device)
+        fT = dict(dtype=torch.float32 if f32 else torch.float64, device=q.device)
         if pose:
             out["pose"] = buffers["pose"] if "pose" in buffers else torch.zeros(b.S, b.N, 24, 3, **f64)
             eo.pose = out["pose"].data_ptr()
         if resid:
-            out["resid"] = buffers["resid"] if "resid" in buffers else torch.zeros(b.S, b.N, b.C, 24, b.W, 2, **f64)
+            out["resid"] = buffers["resid"] if "resid" in buffers else torch.zeros(b.S, b.N, b.C, 24, b.W, 2, **fT)
+            assert out["resid"].dtype == fT["dtype"]
             eo.resid = out["resid"].data_ptr()
         if constraints:
             out["c_eq"] = self.c_eq if hasattr(self, "c_eq") else torch.zeros(b.S, b.N, 26, **f64)
             out["v_in"] = self.v_in if hasattr(self, "v_in") else torch.zeros(b.S, b.N, self.m.n_ineq, **f64)
             eo.c_eq, eo.v_in = out["c_eq"].data_ptr(), out["v_in"].data_ptr()
         if jac:
-            out["jac"] = buffers["jac"] if "jac" in buffers else torch.zeros(b.S, b.N, b.C, self.m.jac_width, **f64)
+            out["jac"] = buffers["jac"] if "jac" in buffers else torch.zeros(b.S, b.N, b.C, self.m.jac_width, **fT)
+            assert out["jac"].dtype == fT["dtype"]
             eo.jac = out["jac"].data_ptr()
         bs = b.struct()
         st = _stream()
-        _lib.check(self.lib.cpe_eval_f64(C.byref(self.m.struct), C.byref(bs), _ptr(q), C.byref(eo), st), "cpe_eval_f64")
+        fn, name = (self.lib.cpe_eval_f32, "cpe_eval_f32") if f32 else (self.lib.cpe_eval_f64, "cpe_eval_f64")
+        _lib.check(fn(C.byref(self.m.struct), C.byref(bs), _ptr(q), C.byref(eo), st), name)
         cost = self.cost if cost_out is None else cost_out
         _lib.check(self.lib.cpe_reduce_cost_f64(C.byref(bs), _ptr(self.frame_cost), _ptr(cost), st), "cpe_reduce_cost_f64")
         self.launches += 2
@@ -200,7 +221,9 @@ class Solver:
         """Lean K1 launch for wave loops: residuals + chain-sparse Jacobian into preallocated `buffers`
         ("resid", "jac"), then the per-sequence cost reduction into cost_out[S,4].  `record_mid` (a CUDA event)
         is recorded between the two kernels so that the K1 launch can be timed on its own."""
-        eo = _lib.CpeEvalOut()
+        f32 = any(t.dtype == torch.float32 for t in buffers.values())
+        assert all((t.dtype == torch.float32) == f32 for t in buffers.values())
+        eo = _lib.CpeEvalOutF32() if f32 else _lib.CpeEvalOut()
         eo.frame_cost = self.frame_cost.data_ptr()
         if "resid" in buffers:
             eo.resid = buffers["resid"].data_ptr()
@@ -208,7 +231,8 @@ class Solver:
             eo.jac = buffers["jac"].data_ptr()
         bs = self.b.struct()
         st = _stream()
-        _lib.check(self.lib.cpe_eval_f64(C.byref(self.m.struct), C.byref(bs), _ptr(q), C.byref(eo), st), "cpe_eval_f64")
+        fn, name = (self.lib.cpe_eval_f32, "cpe_eval_f32") if f32 else (self.lib.cpe_eval_f64, "cpe_eval_f64")
+        _lib.check(fn(C.byref(self.m.struct), C.byref(bs), _ptr(q), C.byref(eo), st), name)
         if record_mid is not None:
             record_mid.record()
         _lib.check(self.lib.cpe_reduce_cost_f64(C.byref(bs), _ptr(self.frame_cost), _ptr(cost_out), st),
@@ -325,7 +349,8 @@ class HostEvaluator:
         self.stage = []
         for _ in range(2):
             st = dict(q=torch.empty(wave, self.N, 54, **f64),
-                      meas=torch.empty(wave, self.N, self.C, 24, self.W, 4, dtype=proto.meas.dtype, device=dev),
+                      meas=torch.empty(wave, self.N, self.C, 24, self.W, proto.meas.shape[5], dtype=proto.meas.dtype,
+                                       device=dev),
                       frame_cost=torch.zeros(wave, self.N, 4, **f64), cost=torch.zeros(wave, 4, **f64),
                       jac=torch.empty(wave, self.N, self.C, model.jac_width, **f64) if jac else None)
             self.stage.append(st)
@@ -333,11 +358,11 @@ class HostEvaluator:
         self.launches = 0
 
     def bytes_per_call(self):
-        h2d = self.S * self.N * (54 * 8 + self.C * 24 * self.W * 4 * self.proto.meas.element_size())
+        h2d = self.S * self.N * (54 * 8 + self.C * 24 * self.W * self.proto.meas.shape[5] * self.proto.meas.element_size())
         return h2d, self.S * 4 * 8
 
     def __call__(self, h_q, h_meas):
-        """h_q[S,N,54] f64 and h_meas[S,N,C,24,W,4] pinned host tensors -> pinned cost[S,4] (valid after return)."""
+        """h_q[S,N,54] f64 and h_meas[S,N,C,24,W,4|3] pinned host tensors -> pinned cost[S,4] (valid after return)."""
         assert not h_q.is_cuda and not h_meas.is_cuda and h_q.is_pinned() and h_meas.is_pinned()
         cur = torch.cuda.current_stream()
         for st in self.streams:

@@ -205,10 +205,12 @@ def make_problem(S=1, N=100, C=6, seed=0, fps=120.0, animal="jules", projector=N
 
 
 def make_device_problem(S, N=500, C=6, seed=0, fps=120.0, animal="jules", device="cuda", n_unique=32, chunk=256,
-                        outlier_frac=0.10, image_size=(1920, 1080)):
+                        outlier_frac=0.10, image_size=(1920, 1080), dlc_native=False):
     """The large sweep built directly in HBM: `n_unique` distinct trajectories / camera rings are
     generated on the host exactly as in make_problem, projected once by the CUDA kernel, tiled to S sequences, and
     the per-sequence detection noise, likelihoods and outliers are drawn on the device (torch generator).
+    With dlc_native=True the detections are kept as DLC triples (x, y, likelihood) -- CPE_MEAS_F32X3, gated on the
+    device -- instead of the pre-gated float4 records; both describe the same problem.
     Returns (Batch, q_true[S,N,54], q_init[S,N,54]) as device tensors."""
     import torch
     from . import engine
@@ -224,7 +226,7 @@ def make_device_problem(S, N=500, C=6, seed=0, fps=120.0, animal="jules", device
     gen = torch.Generator(device=dev)
     gen.manual_seed(int(seed) + 12345)
     sigma = torch.as_tensor(1.0 / sk.measurement_weights()[0] / 2.0, device=dev)               # [24]
-    meas = torch.empty(S, N, C, 24, 1, 4, dtype=torch.float32, device=dev)
+    meas = torch.empty(S, N, C, 24, 1, 3 if dlc_native else 4, dtype=torch.float32, device=dev)
     idx_all = torch.arange(S, device=dev) % nu
     W_, H_ = image_size
     for s0 in range(0, S, chunk):
@@ -248,8 +250,11 @@ def make_device_problem(S, N=500, C=6, seed=0, fps=120.0, animal="jules", device
         det = torch.where(outside[..., None], torch.zeros_like(det), det)
         m = meas[s0:s1, :, :, :, 0]
         m[..., 0:2] = det.to(torch.float32)
-        m[..., 2] = (lik > 0.5).to(torch.float32)
-        m[..., 3] = 0.0
+        if dlc_native:
+            m[..., 2] = lik.to(torch.float32)
+        else:
+            m[..., 2] = (lik > 0.5).to(torch.float32)
+            m[..., 3] = 0.0
     q_true_u = torch.as_tensor(q_u, device=dev)
     q_true = q_true_u[idx_all].contiguous()
     q_init = torch.zeros_like(q_true)

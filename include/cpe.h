@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 102          /* 0.1.2 */
+#define CPE_VERSION 103          /* 0.1.3 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -54,6 +54,12 @@ extern "C" {
 
 #define CPE_CAM_FISHEYE 0        /* acinoset_misc.py:1663-1679 */
 #define CPE_CAM_PINHOLE 1        /* acinoset_misc.py:1682-1696 */
+
+/* layouts of cpe_batch.meas, one record per (sequence, frame, camera, marker, hypothesis) */
+#define CPE_MEAS_F32X4 0         /* float4  {u, v, gate, unused}, gate = likelihood > dlc_thresh ? 1 : 0 packed on the host */
+#define CPE_MEAS_F64X4 1         /* double4 {u, v, gate, unused} */
+#define CPE_MEAS_F32X3 2         /* float3  {x, y, likelihood}: the DLC-native triple (acinoset_misc.py:237-256); the
+                                    strict test likelihood > dlc_thresh (acinoset_misc.py:231) runs on the device */
 
 #define CPE_E_ARG (-1)
 #define CPE_E_DIM (-2)
@@ -99,12 +105,13 @@ typedef struct cpe_model {
 typedef struct cpe_batch {
     int32_t S, N, C, W;
     int32_t cam_model;              /* CPE_CAM_FISHEYE / CPE_CAM_PINHOLE */
-    int32_t meas_is_f64;            /* 0: meas is float4 {u,v,gate,_}; 1: double4 */
+    int32_t meas_layout;            /* CPE_MEAS_* */
+    double dlc_thresh;              /* likelihood threshold of CPE_MEAS_F32X3 (reference default 0.5) */
     double mu_eq, mu_in;            /* augmented-Lagrangian penalties */
     double loss_a, loss_b, loss_c;  /* redescending loss break points (3, 10, 20) */
     const int32_t *n_frames;        /* [S] frames used of each sequence (<= N) */
     const double *h;                /* [S] time step 1/fps (acinoset_opt.py:483-487, 508) */
-    const void *meas;               /* [S,N,C,24,W] x 4 : u, v, gate (likelihood > thresh ? 1 : 0), unused */
+    const void *meas;               /* [S,N,C,24,W] records in meas_layout */
     const double *cams;             /* [S,C,24]  see CPE_CAM_STRIDE */
     const double *chain_vec;        /* [S,24,5,3] body-frame vectors of the marker chains */
     const double *lam_eq;           /* [S,N,26] multipliers (may be NULL = 0) */
@@ -123,6 +130,16 @@ typedef struct cpe_eval_out {
                                        (du/dq_j, dv/dq_j) pair per column j, columns = base x,y,z then
                                        (phi,theta,psi) of each chain link in chain order.  Independent of w. */
 } cpe_eval_out;
+
+/* Outputs of the FP32 flavour: residuals and Jacobian in float, everything else as above. */
+typedef struct cpe_eval_out_f32 {
+    double *frame_cost;             /* [S,N,4] (per-thread loss in float, summed in double) */
+    double *pose;                   /* [S,N,24,3] (FP64: the FK front end is FP64 in both flavours) */
+    float *resid;                   /* [S,N,C,24,W,2] */
+    double *c_eq;                   /* [S,N,26] */
+    double *v_in;                   /* [S,N,n_ineq] */
+    float *jac;                     /* [S,N,C,2*(72+n_u)] same packing as cpe_eval_out.jac */
+} cpe_eval_out_f32;
 
 /* Outputs of cpe_assemble: the per-frame reduced normal equations after Marquardt damping and elimination. */
 typedef struct cpe_assemble_out {
@@ -147,6 +164,12 @@ int cpe_version(void);
 
 /* K1: FK + projection + robust loss (+ optional chain-sparse Jacobian). q[S,N,54]. */
 int cpe_eval_f64(const cpe_model *model, const cpe_batch *batch, const double *q, const cpe_eval_out *out,
+                 void *stream);
+
+/* K1, scaled FP32 flavour: marker offsets relative to the base origin, camera translation and principal-point
+ * minus detection folded in FP64, then projection / residual / loss / Jacobian in FP32 (per-residual error <= 1e-4
+ * relative to max(|r|, 1 px); see tests/test_gpu_parity.py). */
+int cpe_eval_f32(const cpe_model *model, const cpe_batch *batch, const double *q, const cpe_eval_out_f32 *out,
                  void *stream);
 
 /* Deterministic per-sequence reduction of frame_cost[S,N,4] -> cost[S,4] (fixed order). */

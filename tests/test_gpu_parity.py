@@ -238,3 +238,86 @@ def test_solver_converges_like_oracle(gpu):
             return 1000 * np.linalg.norm(a - b, axis=-1).mean()
         assert abs(mpjpe(pg, pt) - mpjpe(pr, pt)) < 1.0, (mpjpe(pg, pt), mpjpe(pr, pt))
         assert np.abs(res["c_eq"][s].cpu().numpy()).max() < 1e-4
+
+
+# FP32 flavour (north star: "<= 1e-4 in FP32").  Tolerances, written out:
+#   residual  |r32 - r64| <= 1e-4 * max(|r64|, 1 px)          (the FP32 floor at ~1000 px offsets is ~6e-5 px)
+#   Jacobian  |J32 - J64| <= 1e-4 * max(row max |J64|, 1)
+#   cost      relative 1e-4 on the measurement term; the FP64 terms (model, joints, inequalities) stay at 1e-9
+RTOL32 = 1e-4
+
+
+@pytest.mark.parametrize("S,N,C", [(2, 7, 6), (2, 5, 4), (1, 9, 1)])
+def test_f32_flavour_matches_oracle(gpu, S, N, C):
+    import torch
+    from cheetah_pose_estimation_b200 import skeleton
+    from oracle import adapters, cameras, cost, kinematics
+    prob, batch, solver, q, qd = _setup(gpu, S=S, N=N, C=C, seed=17)
+    out = solver.evaluate(qd, pose=True, resid=True, jac=True, constraints=True, f32=True)
+    torch.cuda.synchronize()
+    assert out["resid"].dtype == torch.float32 and out["jac"].dtype == torch.float32
+    dense = skeleton.jacobian_to_dense(out["jac"].cpu().numpy().astype(np.float64))
+    for s in range(S):
+        pb = adapters.from_synthetic(prob, s)
+        pose = kinematics.fk(q[s], pb.chain_link, pb.chain_vec)
+        assert _rel(out["pose"][s].cpu().numpy(), pose) < 1e-13              # FK front end is FP64 in both flavours
+        r = cost.residuals(pb, q[s])
+        got = out["resid"][s].cpu().numpy().astype(np.float64)
+        assert (np.abs(got - r) / np.maximum(np.abs(r), 1.0)).max() < RTOL32
+        ref = cost.cost_terms(pb, q[s])
+        c = out["cost"][s].cpu().numpy()
+        assert abs(c[0] - ref[0]) <= RTOL32 * abs(ref[0])
+        assert np.allclose(c[1:], ref[1:], rtol=RTOL, atol=1e-9)
+        G = kinematics.fk_jacobian(q[s], pb.chain_link, pb.chain_vec)
+        P = cameras.project_jacobian(pose[:, None], pb.cams[None, :, None, :])
+        J = np.einsum("ncldi,nlia->nclda", P, G)
+        scale = np.abs(J).max(axis=-1, keepdims=True)
+        assert (np.abs(dense[s] - J) / np.maximum(scale, 1.0)).max() < RTOL32
+
+
+def test_f32_flavour_far_from_origin(gpu):
+    """The scaled path must not lose accuracy when the animal is 40 m from the world origin (cameras moved along)."""
+    import torch
+    from cheetah_pose_estimation_b200 import engine
+    from oracle import adapters, cost
+    prob, batch, solver, q, qd = _setup(gpu, S=1, N=6, C=6, seed=23)
+    shift = np.array([40.0, -25.0, 3.0])
+    q2 = q.copy()
+    q2[..., 0:3] += shift
+    cams = prob.cams.copy()
+    for c in range(cams.shape[1]):
+        R = cams[0, c, 8:17].reshape(3, 3)
+        cams[0, c, 17:20] -= R @ shift
+    batch2 = engine.Batch.from_numpy(prob.meas, cams, prob.chain_vec, prob.h)
+    s2 = engine.Solver(gpu, batch2, with_solver=False)
+    out = s2.evaluate(torch.as_tensor(q2, device="cuda:0"), resid=True, f32=True)
+    pb = adapters.from_synthetic(prob, 0)
+    r = cost.residuals(pb, q[0])                                             # same residuals as the unshifted problem
+    got = out["resid"][0].cpu().numpy().astype(np.float64)
+    assert (np.abs(got - r) / np.maximum(np.abs(r), 1.0)).max() < RTOL32
+
+
+def test_dlc_native_layout_equals_pregated(gpu):
+    """CPE_MEAS_F32X3 (x, y, likelihood; strict `> dlc_thresh` on the device) gives bit-identical costs,
+    residuals and LM steps to the host-gated float4 records."""
+    import torch
+    from cheetah_pose_estimation_b200 import engine
+    prob, batch, solver, q, qd = _setup(gpu, S=2, N=8, C=6, seed=29)
+    rng = np.random.default_rng(2)
+    lik = rng.random(prob.meas.shape[:-1]).astype(np.float32)
+    lik[0, 0, 0, :4, 0] = 0.5                                                # exactly at the threshold: gate off
+    m3 = np.concatenate([prob.meas[..., 0:2], lik[..., None]], -1).astype(np.float32)
+    m4 = prob.meas.copy()
+    m4[..., 2] = (lik > 0.5).astype(np.float32)
+    b3 = engine.Batch.from_numpy(m3, prob.cams, prob.chain_vec, prob.h, dlc_native=True)
+    b4 = engine.Batch.from_numpy(m4, prob.cams, prob.chain_vec, prob.h)
+    assert b3.meas_layout == engine.MEAS_F32X3 and b4.meas_layout == engine.MEAS_F32X4
+    s3, s4 = engine.Solver(gpu, b3), engine.Solver(gpu, b4)
+    o3 = s3.evaluate(qd, resid=True, jac=True)
+    o4 = s4.evaluate(qd, resid=True, jac=True)
+    for k in ("cost", "resid", "jac"):
+        assert torch.equal(o3[k], o4[k]), k
+    damp = torch.full((2,), 1e-2, dtype=torch.float64, device="cuda:0")
+    d3 = s3.lm_step(qd, damp)[0].clone()
+    d4 = s4.lm_step(qd, damp)[0].clone()
+    assert torch.equal(d3, d4)
