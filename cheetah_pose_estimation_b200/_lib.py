@@ -19,7 +19,7 @@ class CpeModel(C.Structure):
         ("chain_link", c_i32p), ("eq_pairs", c_i32p), ("ineq_idx", c_i32p),
         ("ineq_bounds", c_f64p), ("wq", c_f64p), ("meas_w", c_f64p), ("ind_idx", c_i32p), ("ind_pos", c_i32p),
         ("grp_ndep", c_i32p), ("grp_nnb", c_i32p), ("grp_dep", c_i32p), ("grp_nb", c_i32p),
-        ("u_off", c_i32p), ("u_item", c_i32p),
+        ("u_off", c_i32p), ("u_item", c_i32p), ("col_item", c_i32p),
         ("ent_pq", c_i32p), ("a_ptr", c_i32p), ("a_items", c_i32p), ("e_ptr", c_i32p), ("e_items", c_i32p),
         ("i_ptr", c_i32p), ("i_items", c_i32p), ("diag_ent", c_i32p), ("grad_ent", c_i32p), ("grp_src", c_i32p),
         ("s_src", c_i32p), ("s_ptr", c_i32p), ("s_items", c_i32p),

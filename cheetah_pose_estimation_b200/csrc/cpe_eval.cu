@@ -18,16 +18,18 @@
 // (cx - u_meas) before rounding, so the residual does not lose the ~1000 px offset either.  Per (camera, marker):
 // projection, residual, robust loss and the Jacobian columns J = dproj(2x3) . [I | U] run in T.
 //
-// Mapping (sm_100a): one CTA owns F consecutive frames of ONE sequence (F*C*24 <= 160 threads).  Phases:
-//   A  q, cameras -> shared; detections prefetched into registers (coalesced)
-//   B  one thread per link: 3 sincos + rotation matrix (FP64)
-//   C  warp-uniform item lists: chain derivative blocks U = dR/dangle . v (one item per (marker, link): 3 angles),
-//      marker offsets, camera translations, joint equalities, inequalities, motion terms
-//   D  one thread per (frame, camera, marker): projection, residuals, loss, Jacobian columns into a shared staging
-//      tile laid out exactly like the packed global Jacobian
-//   E  the tile leaves the SM as ONE bulk async copy (cp.async.bulk, the TMA engine) while warps reduce the costs.
-// No atomics: every reduction has a fixed order, so a sequence's results are bit-identical whatever its batch
-// neighbours are.
+// Mapping (sm_100a): ONE WARP PER FRAME.  A CTA is WPC independent warps working on WPC consecutive frames of one
+// sequence; after the cameras are staged (the only CTA barrier) a warp never waits for another warp.  Per frame:
+//   A  q -> the warp's shared slice; first 32 detections prefetched into registers (coalesced)
+//   B  51 sincos (2 rounds over the lanes), 17 rotation matrices, FP64
+//   C  rounds of warp-uniform items: chain derivative blocks U = dR/dangle . v (one item per (marker, link)),
+//      marker offsets, camera translations, joint equalities, inequalities, motion terms; the cost terms stay in
+//      lane registers
+//   D  rounds of 32 (camera, marker) pairs: projection, residuals, loss, Jacobian columns written straight from
+//      registers (the 32 marker blocks of a round are one contiguous span of the packed Jacobian; L2 merges the
+//      16-byte pieces into full lines before they reach HBM); the next round's detections are in flight meanwhile
+//   E  fixed-order shuffle reductions -> frame_cost
+// No atomics, no cross-warp reductions: a sequence's results are bit-identical whatever its batch neighbours are.
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
@@ -43,28 +45,28 @@ struct EvalParams {
     cpe_batch b;
     const double *q;
     cpe_eval_out eo;        // resid / jac are T* (float for the f32 flavour)
-    int F;                  // frames per CTA
-    int TPF;                // threads per frame = C * 24
-    int chunks;             // ceil(N / F)
+    int TPF;                // (camera, marker) pairs per frame = C * 24
+    int chunks;             // ceil(N / WPC)
     int n_u;                // packed chain columns per marker set (198 for the cheetah)
     int n_pair;             // n_u / 3 (marker, link) pairs
-    int i_mk, i_tc, i_eq, i_in, i_mo, i_end;   // warp-aligned item list boundaries of phase C
-    int fd;                 // per-frame FP64 shared stride (doubles)
-    int ft;                 // per-frame T shared stride (elements)
-    int off_t;              // byte offset of the T region
-    int off_stage;          // byte offset of the Jacobian staging tile
+    int nitem;              // 24 + n_pair Jacobian items (3 columns each) per frame.view
+    unsigned item_magic;    // ceil(2^24 / nitem): g / nitem == (g * item_magic) >> 24 for g < C * nitem
+    int wbytes;             // bytes of one warp's shared slice
+    int off_warp;           // byte offset of the first warp slice (after the camera rows)
     double ea, eb, ec;      // exp(loss_a), exp(loss_b), exp(loss_c)
 };
 
-// per-frame FP64 shared layout (doubles): q, rotations, cost contributions eq[26] in[32] mo[54] me[TPF]
-constexpr int QO = 0, RO = 56, CTR = 210;
-constexpr int EQC = 0, INC = 26, MOC = 58, MEC = 112;
-// per-frame T shared layout (elements): sin/cos, marker offsets, camera translations, U blocks
-constexpr int T_SC = 0, T_POS = 104, T_TC = 176, T_U = 200;
+// per-warp FP64 slice (doubles): q, sin/cos, rotations
+constexpr int QO = 0, SCO = 56, RO = 160, WD = 314;
+// per-warp T slice (elements): marker offsets, camera translations, U = 3x3 blocks padded to 10 (block 0 = identity,
+// block 1 + k = dR/d(phi,theta,psi) . v of (marker, link) pair k); the f32 flavour also keeps a float copy of sin/cos
+// in front.  The d(u,v)/d(point) rows of the 32 pairs of
+// a round (6 T each) reuse the sin/cos + rotation doubles, which are dead after phase C.
+constexpr int T_POS = 0, T_TC = 72, T_U = 96;
 
 template <typename T> struct Vec;
-template <> struct Vec<double> { using t2 = double2; static constexpr int UPAD = 8; };
-template <> struct Vec<float> { using t2 = float2; static constexpr int UPAD = 8; };
+template <> struct Vec<double> { using t2 = double2; };
+template <> struct Vec<float> { using t2 = float2; };
 
 __device__ __forceinline__ double2 mk2(double a, double b) { return make_double2(a, b); }
 __device__ __forceinline__ float2 mk2(float a, float b) { return make_float2(a, b); }
@@ -87,268 +89,241 @@ __device__ __forceinline__ T redescending_value(T E, T a, T b, T c, T ea, T eb, 
     return (T(1) - sa) * T(0.5) * E * E + (sa - sb) * p2 + (sb - sc) * p3 + sc * k4;
 }
 
-template <typename T, bool JAC, int MAXT, int MINB>
-__global__ void __launch_bounds__(MAXT, MINB) eval_kernel(const __grid_constant__ EvalParams p) {
+template <typename T, bool JAC, int WPC, int MINB>
+__global__ void __launch_bounds__(WPC * 32, MINB) eval_kernel(const __grid_constant__ EvalParams p) {
     using T2 = typename Vec<T>::t2;
-    constexpr int UPAD = Vec<T>::UPAD;
     constexpr bool F64 = sizeof(T) == 8;
+    constexpr int TS0 = F64 ? 0 : 104;                     // f32: float copy of sin/cos in front of the T slice
     extern __shared__ __align__(16) unsigned char smraw[];
-    const int tid = threadIdx.x;
-    const int N = p.b.N, C = p.b.C, W = p.b.W, F = p.F, TPF = p.TPF;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int N = p.b.N, C = p.b.C, W = p.b.W, TPF = p.TPF;
     const int s = blockIdx.x / p.chunks;
-    const int k0 = (blockIdx.x - s * p.chunks) * F;
-    const int nf = p.b.n_frames[s];
-    if (k0 >= nf) return;
-    const int nv = min(F, nf - k0);                       // valid frames of this CTA
-    const int n_ineq = p.m.n_ineq, n_u = p.n_u;
+    const int k = (blockIdx.x - s * p.chunks) * WPC + warp;
     double *camd = reinterpret_cast<double *>(smraw);      // [C*24] FP64 camera rows
-    double *frd0 = camd + C * CPE_CAM_STRIDE;              // per-frame FP64 regions
-    T *camt = F64 ? reinterpret_cast<T *>(camd) : reinterpret_cast<T *>(smraw + p.off_t);   // [C*24] in T
-    T *frt0 = reinterpret_cast<T *>(smraw + p.off_t) + (F64 ? 0 : C * CPE_CAM_STRIDE);
-    T *stage = reinterpret_cast<T *>(smraw + p.off_stage);  // [F][C][540]
-    const int f0 = s * N + k0;                            // global index of the first frame
-    const int jw = 2 * (72 + n_u);                        // packed Jacobian elements per frame.view
-
-    // Every thread belongs to ONE frame of the CTA in phases A and D: frame mf, local index mt in [0, TPF).
-    int mf = 0, mt = tid;
-    if (F > 1) { mf = tid / TPF; mt = tid - mf * TPF; }
-    const bool mvalid = mf < nv && mt < TPF;
-    const int fidx = f0 + mf;
-    const int mc = mt / 24, ml = mt - mc * 24;
-    const size_t midx0 = ((size_t)(fidx * C + mc) * 24 + ml) * W;
-    // ---- A: issue the detection load before the FK phases; q and cameras to shared --------------------------------
-    MeasRaw mraw;
-    mraw.d = make_double4(0.0, 0.0, 0.0, 0.0);
-    if (mvalid) meas_fetch(p.b, midx0, mraw);
-    for (int i = tid; i < nv * 54; i += blockDim.x) {
-        const int f = i / 54, c = i - f * 54;
-        frd0[f * p.fd + QO + c] = p.q[(size_t)(f0 + f) * 54 + c];
-    }
-    for (int i = tid; i < C * CPE_CAM_STRIDE; i += blockDim.x) {
+    T *camt = F64 ? reinterpret_cast<T *>(camd) : reinterpret_cast<T *>(smraw + sizeof(double) * C * CPE_CAM_STRIDE);
+    int32_t *coltab = reinterpret_cast<int32_t *>(smraw + p.off_warp) - ((p.nitem + 3) & ~3);   // [nitem] Jacobian items
+    for (int i = tid; i < C * CPE_CAM_STRIDE; i += WPC * 32) {
         const double v = p.b.cams[(size_t)s * C * CPE_CAM_STRIDE + i];
         camd[i] = v;
         if (!F64) camt[i] = (T)v;
     }
-    __syncthreads();
-    // ---- B: one thread per (frame, link): sincos of its three angles + rotation matrix, FP64 ------------------------
-    if (tid < nv * 17) {
-        const int f = tid / 17, link = tid - f * 17;
-        double *frd = frd0 + f * p.fd;
-        T *frt = frt0 + f * p.ft;
-        double sc[6];
-        sincos(frd[QO + 3 + 3 * link + 0], &sc[0], &sc[1]);
-        sincos(frd[QO + 3 + 3 * link + 1], &sc[2], &sc[3]);
-        sincos(frd[QO + 3 + 3 * link + 2], &sc[4], &sc[5]);
-        double M[9];
-        rot_from_sc(sc, M);
-#pragma unroll
-        for (int i = 0; i < 9; ++i) frd[RO + 9 * link + i] = M[i];
-#pragma unroll
-        for (int i = 0; i < 6; ++i) frt[T_SC + 6 * link + i] = (T)sc[i];
-    }
-    __syncthreads();
+    if (JAC) for (int i = tid; i < p.nitem; i += WPC * 32) coltab[i] = p.m.col_item[i];
+    __syncthreads();                                       // the only CTA-wide barrier
+    const int nf = p.b.n_frames[s];
+    if (k >= nf) return;
+    double *wd = reinterpret_cast<double *>(smraw + p.off_warp + warp * p.wbytes);
+    T *wt = reinterpret_cast<T *>(wd + WD);
+    const T *sct = F64 ? reinterpret_cast<const T *>(wd + SCO) : wt;
+    T *pos = wt + TS0 + T_POS, *tcv = wt + TS0 + T_TC, *U = wt + TS0 + T_U;
+    T *dp = reinterpret_cast<T *>(wd + SCO);               // [32][6] per-round projection derivatives (phase D)
+    const int fi = s * N + k;                              // global frame index
+    const int n_ineq = p.m.n_ineq;
+    const size_t m0 = (size_t)fi * TPF;                    // detection record of (camera 0, marker 0), in units of W
 
-    // ---- C: camera-independent per-frame items, in warp-uniform lists ------------------------------------------------
+    // ---- A: q -> shared; first detections in flight ----------------------------------------------------------------
+    MeasRaw cur;
+    cur.d = make_double4(0.0, 0.0, 0.0, 0.0);
+    if (lane < TPF) meas_fetch(p.b, (m0 + lane) * W, cur);
+    const double *qf = p.q + (size_t)fi * 54;
+    for (int c = lane; c < 54; c += 32) wd[QO + c] = qf[c];
+    __syncwarp();
+    // ---- B: sin/cos of the 51 angles, then the 17 link rotations (FP64) --------------------------------------------
+    for (int a = lane; a < 51; a += 32) {
+        double sn, cs;
+        sincos(wd[QO + 3 + a], &sn, &cs);
+        wd[SCO + 2 * a] = sn; wd[SCO + 2 * a + 1] = cs;
+        if (!F64) { wt[2 * a] = (T)sn; wt[2 * a + 1] = (T)cs; }
+    }
+    __syncwarp();
+    if (lane < 17) rot_from_sc(wd + SCO + 6 * lane, wd + RO + 9 * lane);
+    __syncwarp();
+
+    // ---- C: camera-independent per-frame items, one warp-uniform round per kind ---------------------------------------
+    double a_eq = 0.0, a_in = 0.0, a_mo = 0.0;
     {
         const double *cvec = p.b.chain_vec + (size_t)s * 24 * CPE_MAX_CHAIN * 3;
         const int32_t *chain_link = p.m.chain_link;
-        const int i_begin = JAC ? 0 : p.i_mk;
-        const int per = p.i_end - i_begin;
-        for (int w0 = tid; w0 < nv * per; w0 += blockDim.x) {
-            int f = 0, it = w0;
-            if (F > 1) { f = w0 / per; it = w0 - f * per; }
-            it += i_begin;
-            double *frd = frd0 + f * p.fd;
-            T *frt = frt0 + f * p.ft;
-            double *ctr = frd + CTR;
-            const int fi = f0 + f;
-            if (it < p.i_mk) {
-                // U block of one (marker, chain link): 3 angles x 3 components (8 stored)
-                if (it < p.n_pair) {
-                    const int code = p.m.u_item[3 * it];
-                    const int l = code >> 8, j = (code >> 4) & 15;
-                    const int link = chain_link[l * CPE_MAX_CHAIN + j];
+        if (JAC) {
+            // U: identity columns, then one block per (marker, chain link): 3 angles x 3 components
+            if (lane < 10) U[lane] = (lane == 0 || lane == 4 || lane == 8) ? T(1) : T(0);
+            for (int it = lane; it < p.n_pair; it += 32) {
+                const int code = p.m.u_item[3 * it];
+                const int l = code >> 8, j = (code >> 4) & 15;
+                const int link = chain_link[l * CPE_MAX_CHAIN + j];
+                const double *v = cvec + (l * CPE_MAX_CHAIN + j) * 3;
+                T o[9];
+                drot_all<T>(sct + 6 * link, (T)v[0], (T)v[1], (T)v[2], o);
+                T *u = U + 10 + 10 * it;                 // rows = angle, columns = xyz
+#pragma unroll
+                for (int i = 0; i < 9; ++i) u[i] = o[i];
+            }
+        }
+        if (lane < 24) {
+            // marker offset from the base origin (FP64 accumulate; the FP32 flavour never sees world metres)
+            const int l = lane;
+            double x = 0.0, y = 0.0, z = 0.0;
+#pragma unroll
+            for (int j = 0; j < CPE_MAX_CHAIN; ++j) {
+                const int link = chain_link[l * CPE_MAX_CHAIN + j];
+                if (link >= 0) {
+                    const double *Rl = wd + RO + link * 9;
                     const double *v = cvec + (l * CPE_MAX_CHAIN + j) * 3;
-                    T o[9];
-                    drot_all<T>(frt + T_SC + 6 * link, (T)v[0], (T)v[1], (T)v[2], o);
-                    T *u = frt + T_U + UPAD * it;                 // o[8] = dz/dpsi = 0 is not stored
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) u[i] = o[i];
+                    const double v0 = v[0], v1 = v[1], v2 = v[2];
+                    x += Rl[0] * v0 + Rl[1] * v1 + Rl[2] * v2;
+                    y += Rl[3] * v0 + Rl[4] * v1 + Rl[5] * v2;
+                    z += Rl[6] * v0 + Rl[7] * v1 + Rl[8] * v2;
                 }
-            } else if (it < p.i_tc) {
-                const int l = it - p.i_mk;
-                if (l < 24) {
-                    // marker offset from the base origin (FP64 accumulate; the FP32 flavour never sees world metres)
-                    double x = 0.0, y = 0.0, z = 0.0;
-#pragma unroll
-                    for (int j = 0; j < CPE_MAX_CHAIN; ++j) {
-                        const int link = chain_link[l * CPE_MAX_CHAIN + j];
-                        if (link >= 0) {
-                            const double *Rl = frd + RO + link * 9;
-                            const double *v = cvec + (l * CPE_MAX_CHAIN + j) * 3;
-                            const double v0 = v[0], v1 = v[1], v2 = v[2];
-                            x += Rl[0] * v0 + Rl[1] * v1 + Rl[2] * v2;
-                            y += Rl[3] * v0 + Rl[4] * v1 + Rl[5] * v2;
-                            z += Rl[6] * v0 + Rl[7] * v1 + Rl[8] * v2;
-                        }
-                    }
-                    frt[T_POS + l * 3 + 0] = (T)x; frt[T_POS + l * 3 + 1] = (T)y; frt[T_POS + l * 3 + 2] = (T)z;
-                    if (p.eo.pose) {
-                        double *o = p.eo.pose + ((size_t)fi * 24 + l) * 3;
-                        o[0] = frd[QO + 0] + x; o[1] = frd[QO + 1] + y; o[2] = frd[QO + 2] + z;
-                    }
-                }
-            } else if (it < p.i_eq) {
-                const int e = it - p.i_tc;
-                if (e < 3 * C) {
-                    // base origin in the camera frame: tc = R_c base + t_c (FP64)
-                    const int c = e / 3, r = e - 3 * c;
-                    const double *cm = camd + c * CPE_CAM_STRIDE;
-                    frt[T_TC + e] = (T)(cm[8 + 3 * r] * frd[QO + 0] + cm[9 + 3 * r] * frd[QO + 1] +
-                                        cm[10 + 3 * r] * frd[QO + 2] + cm[17 + r]);
-                }
-            } else if (it < p.i_in) {
-                const int e = it - p.i_eq;
-                if (e < 26) {
-                    const int4 pr4 = reinterpret_cast<const int4 *>(p.m.eq_pairs)[e];
-                    const double *Ra = frd + RO + pr4.x * 9, *Rb = frd + RO + pr4.y * 9;
-                    const int ia = pr4.z, ib = pr4.w;
-                    const double c = Ra[ia] * Rb[ib] + Ra[3 + ia] * Rb[3 + ib] + Ra[6 + ia] * Rb[6 + ib];
-                    const double lam = p.b.lam_eq ? p.b.lam_eq[(size_t)fi * 26 + e] : 0.0;
-                    const double t = c + lam / p.b.mu_eq;
-                    ctr[EQC + e] = 0.5 * p.b.mu_eq * t * t;
-                    if (p.eo.c_eq) p.eo.c_eq[(size_t)fi * 26 + e] = c;
-                }
-            } else if (it < p.i_mo) {
-                const int j = it - p.i_in;
-                if (j < n_ineq) {
-                    const int ip = p.m.ineq_idx[2 * j], im = p.m.ineq_idx[2 * j + 1];
-                    const double lo = p.m.ineq_bounds[2 * j], up = p.m.ineq_bounds[2 * j + 1];
-                    const double d = frd[QO + ip] - (im >= 0 ? frd[QO + im] : 0.0);
-                    const double lam = p.b.lam_in ? p.b.lam_in[(size_t)fi * n_ineq + j] : 0.0;
-                    const double t = d + lam / p.b.mu_in;
-                    const double v = t - fmin(fmax(t, lo), up);
-                    ctr[INC + j] = 0.5 * p.b.mu_in * v * v;
-                    if (p.eo.v_in) p.eo.v_in[(size_t)fi * n_ineq + j] = v;
-                }
-            } else {
-                const int c = it - p.i_mo;
-                if (c < 54) {
-                    const double w = p.m.wq[c];
-                    double val = 0.0;
-                    if (w != 0.0 && k0 + f >= 3) {
-                        const double h = p.b.h[s];
-                        const double *qf = p.q + (size_t)fi * 54;
-                        const double d3 = (frd[QO + c] - 3.0 * qf[c - 54] + 3.0 * qf[c - 108] - qf[c - 162]) / (h * h);
-                        val = w * d3 * d3;
-                    }
-                    ctr[MOC + c] = val;
+            }
+            pos[l * 3 + 0] = (T)x; pos[l * 3 + 1] = (T)y; pos[l * 3 + 2] = (T)z;
+            if (p.eo.pose) {
+                double *o = p.eo.pose + ((size_t)fi * 24 + l) * 3;
+                o[0] = wd[QO + 0] + x; o[1] = wd[QO + 1] + y; o[2] = wd[QO + 2] + z;
+            }
+        }
+        if (lane < 3 * C) {
+            // base origin in the camera frame: tc = R_c base + t_c (FP64)
+            const int c = lane / 3, r = lane - 3 * c;
+            const double *cm = camd + c * CPE_CAM_STRIDE;
+            tcv[lane] = (T)(cm[8 + 3 * r] * wd[QO + 0] + cm[9 + 3 * r] * wd[QO + 1] + cm[10 + 3 * r] * wd[QO + 2] +
+                            cm[17 + r]);
+        }
+        if (lane < 26) {
+            const int e = lane;
+            const int4 pr4 = reinterpret_cast<const int4 *>(p.m.eq_pairs)[e];
+            const double *Ra = wd + RO + pr4.x * 9, *Rb = wd + RO + pr4.y * 9;
+            const int ia = pr4.z, ib = pr4.w;
+            const double c = Ra[ia] * Rb[ib] + Ra[3 + ia] * Rb[3 + ib] + Ra[6 + ia] * Rb[6 + ib];
+            const double lam = p.b.lam_eq ? p.b.lam_eq[(size_t)fi * 26 + e] : 0.0;
+            const double t = c + lam / p.b.mu_eq;
+            a_eq = 0.5 * p.b.mu_eq * t * t;
+            if (p.eo.c_eq) p.eo.c_eq[(size_t)fi * 26 + e] = c;
+        }
+        if (lane < n_ineq) {
+            const int j = lane;
+            const int ip = p.m.ineq_idx[2 * j], im = p.m.ineq_idx[2 * j + 1];
+            const double lo = p.m.ineq_bounds[2 * j], up = p.m.ineq_bounds[2 * j + 1];
+            const double d = wd[QO + ip] - (im >= 0 ? wd[QO + im] : 0.0);
+            const double lam = p.b.lam_in ? p.b.lam_in[(size_t)fi * n_ineq + j] : 0.0;
+            const double t = d + lam / p.b.mu_in;
+            const double v = t - fmin(fmax(t, lo), up);
+            a_in = 0.5 * p.b.mu_in * v * v;
+            if (p.eo.v_in) p.eo.v_in[(size_t)fi * n_ineq + j] = v;
+        }
+        if (k >= 3) {
+            const double h = p.b.h[s];
+            const double ih2 = 1.0 / (h * h);
+            for (int c = lane; c < 54; c += 32) {
+                const double w = p.m.wq[c];
+                if (w != 0.0) {
+                    const double d3 = (wd[QO + c] - 3.0 * qf[c - 54] + 3.0 * qf[c - 108] - qf[c - 162]) * ih2;
+                    a_mo += w * d3 * d3;
                 }
             }
         }
     }
-    __syncthreads();
+    __syncwarp();
 
-    // ---- D: one thread per (frame, camera, marker): projection, residuals, robust loss, Jacobian columns --------------
-    if (mvalid) {
-        double *frd = frd0 + mf * p.fd;
-        const T *frt = frt0 + mf * p.ft;
+    // ---- D: rounds of 32 (camera, marker) pairs: projection, residuals, robust loss, Jacobian columns -----------------
+    T rho = T(0);
+    {
         const T la_ = (T)p.b.loss_a, lb_ = (T)p.b.loss_b, lc_ = (T)p.b.loss_c;
         const T ea = (T)p.ea, eb = (T)p.eb, ec = (T)p.ec;
-        const T *cm = camt + mc * CPE_CAM_STRIDE;
-        const double *cmd = camd + mc * CPE_CAM_STRIDE;
-        const T dx = frt[T_POS + 3 * ml], dy = frt[T_POS + 3 * ml + 1], dz = frt[T_POS + 3 * ml + 2];
-        const T *tc = frt + T_TC + 3 * mc;
-        const T xc = cm[8] * dx + cm[9] * dy + cm[10] * dz + tc[0];
-        const T yc = cm[11] * dx + cm[12] * dy + cm[13] * dz + tc[1];
-        const T zc = cm[14] * dx + cm[15] * dy + cm[16] * dz + tc[2];
-        ProjT<T> pr;
-        project_cam<T, JAC>(xc, yc, zc, cm, p.b.cam_model, pr);
-        T rho = T(0);
-        const double cmult = cmd[20], cx = cmd[2], cy = cmd[3];
-        for (int w = 0; w < W; ++w) {
-            if (w > 0) meas_fetch(p.b, midx0 + w, mraw);
-            double um, vm, gate;
-            meas_unpack(p.b, mraw, um, vm, gate);
-            const T wgt = (T)(gate * p.m.meas_w[w * 24 + ml] * cmult);
-            // residual = (fx a s) + (cx - u_meas): the ~1000 px offsets cancel in FP64 before rounding to T
-            const T ru = pr.pu + (T)(cx - um), rv = pr.pv + (T)(cy - vm);
-            if (p.eo.resid) reinterpret_cast<T2 *>(p.eo.resid)[midx0 + w] = mk2(ru, rv);
-            rho += redescending_value<T>(fabs(wgt * ru), la_, lb_, lc_, ea, eb, ec);
-            rho += redescending_value<T>(fabs(wgt * rv), la_, lb_, lc_, ea, eb, ec);
-        }
-        frd[CTR + MEC + mt] = (double)rho;
-        if (JAC) {
-            const int uo0 = p.m.u_off[ml], nlk = (p.m.u_off[ml + 1] - uo0) / 3;      // chain links of this marker
-            // marker block of the packed Jacobian: (3 + 3 nlk) columns, each a (du, dv) pair
-            T2 *jc = reinterpret_cast<T2 *>(stage + (size_t)(mf * C + mc) * jw + 2 * (3 * ml + uo0));
-            jc[0] = mk2(pr.du[0], pr.dv[0]);
-            jc[1] = mk2(pr.du[1], pr.dv[1]);
-            jc[2] = mk2(pr.du[2], pr.dv[2]);
-            const T *U = frt + T_U + UPAD * (uo0 / 3);
-            for (int j = 0; j < nlk; ++j) {
-                T u[9];
-                if (F64) {
-                    const double2 *U2 = reinterpret_cast<const double2 *>(U + UPAD * j);
-                    const double2 a0 = U2[0], a1 = U2[1], a2 = U2[2], a3 = U2[3];
-                    u[0] = a0.x; u[1] = a0.y; u[2] = a1.x; u[3] = a1.y; u[4] = a2.x; u[5] = a2.y; u[6] = a3.x; u[7] = a3.y;
-                    u[8] = (T)0;
-                } else {
-                    const float4 *U4 = reinterpret_cast<const float4 *>(U + UPAD * j);
-                    const float4 a0 = U4[0], a1 = U4[1];
-                    u[0] = a0.x; u[1] = a0.y; u[2] = a0.z; u[3] = a0.w; u[4] = a1.x; u[5] = a1.y; u[6] = a1.z; u[7] = a1.w;
-                    u[8] = (T)0;
+        for (int p0 = 0; p0 < TPF; p0 += 32) {
+            const int pi = p0 + lane;
+            MeasRaw nxt;
+            nxt.d = make_double4(0.0, 0.0, 0.0, 0.0);
+            if (pi + 32 < TPF) meas_fetch(p.b, (m0 + pi + 32) * W, nxt);        // next round's detections in flight
+            if (pi < TPF) {
+                const int mc = pi / 24, ml = pi - mc * 24;
+                const T *cm = camt + mc * CPE_CAM_STRIDE;
+                const double *cmd = camd + mc * CPE_CAM_STRIDE;
+                const T dx = pos[3 * ml], dy = pos[3 * ml + 1], dz = pos[3 * ml + 2];
+                const T *tc = tcv + 3 * mc;
+                const T xc = cm[8] * dx + cm[9] * dy + cm[10] * dz + tc[0];
+                const T yc = cm[11] * dx + cm[12] * dy + cm[13] * dz + tc[1];
+                const T zc = cm[14] * dx + cm[15] * dy + cm[16] * dz + tc[2];
+                ProjT<T> pr;
+                project_cam<T, JAC>(xc, yc, zc, cm, p.b.cam_model, pr);
+                const double cmult = cmd[20], cx = cmd[2], cy = cmd[3];
+                const size_t mi = (m0 + pi) * W;
+                for (int w = 0; w < W; ++w) {
+                    if (w > 0) meas_fetch(p.b, mi + w, cur);
+                    double um, vm, gate;
+                    meas_unpack(p.b, cur, um, vm, gate);
+                    const T wgt = (T)(gate * p.m.meas_w[w * 24 + ml] * cmult);
+                    // residual = (fx a s) + (cx - u_meas): the ~1000 px offsets cancel in FP64 before rounding to T
+                    const T ru = pr.pu + (T)(cx - um), rv = pr.pv + (T)(cy - vm);
+                    if (p.eo.resid) reinterpret_cast<T2 *>(p.eo.resid)[mi + w] = mk2(ru, rv);
+                    rho += redescending_value<T>(fabs(wgt * ru), la_, lb_, lc_, ea, eb, ec);
+                    rho += redescending_value<T>(fabs(wgt * rv), la_, lb_, lc_, ea, eb, ec);
                 }
-                T2 *o = jc + 3 + 3 * j;
-                o[0] = mk2(pr.du[0] * u[0] + pr.du[1] * u[1] + pr.du[2] * u[2],
-                           pr.dv[0] * u[0] + pr.dv[1] * u[1] + pr.dv[2] * u[2]);
-                o[1] = mk2(pr.du[0] * u[3] + pr.du[1] * u[4] + pr.du[2] * u[5],
-                           pr.dv[0] * u[3] + pr.dv[1] * u[4] + pr.dv[2] * u[5]);
-                o[2] = mk2(pr.du[0] * u[6] + pr.du[1] * u[7], pr.dv[0] * u[6] + pr.dv[1] * u[7]);   // dz/dpsi = 0
+                if (JAC) {
+                    T2 *d2 = reinterpret_cast<T2 *>(dp + 6 * lane);
+                    d2[0] = mk2(pr.du[0], pr.du[1]);
+                    d2[1] = mk2(pr.du[2], pr.dv[0]);
+                    d2[2] = mk2(pr.dv[1], pr.dv[2]);
+                }
             }
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            if (JAC) {
+                // item pass: the 32 pairs of this round own ONE contiguous span of packed columns; lane <-> item of 3
+                // adjacent columns, so the three stores of a round fill the span without gaps
+                __syncwarp();
+                const int nitem = p.nitem;
+                const int pe = min(p0 + 32, TPF);
+                const int c0 = p0 / 24, l0 = p0 - 24 * c0;
+                const int g0 = c0 * nitem + l0 + p.m.u_off[l0] / 3;
+                int g1 = C * nitem;
+                if (pe < TPF) {
+                    const int c1 = pe / 24, l1 = pe - 24 * c1;
+                    g1 = c1 * nitem + l1 + p.m.u_off[l1] / 3;
+                }
+                T2 *jb = reinterpret_cast<T2 *>(p.eo.jac) + (size_t)fi * C * 3 * nitem;
+                for (int g = g0 + lane; g < g1; g += 32) {
+                    const int c = (int)(((unsigned)g * p.item_magic) >> 24);
+                    const int e = coltab[g - c * nitem];
+                    const int slot = c * 24 + (e >> 16) - p0;
+                    const T2 *d2 = reinterpret_cast<const T2 *>(dp + 6 * slot);
+                    const T2 da = d2[0], db = d2[1], dc = d2[2];       // du0 du1 | du2 dv0 | dv1 dv2
+                    const T2 *u2 = reinterpret_cast<const T2 *>(U + (e & 0xffff));
+                    const T2 ua = u2[0], ub = u2[1], uc = u2[2], ud = u2[3], ue = u2[4];   // u0 u1|u2 u3|u4 u5|u6 u7|u8 -
+                    T2 *o = jb + 3 * (size_t)g;
+                    o[0] = mk2(da.x * ua.x + da.y * ua.y + db.x * ub.x, db.y * ua.x + dc.x * ua.y + dc.y * ub.x);
+                    o[1] = mk2(da.x * ub.y + da.y * uc.x + db.x * uc.y, db.y * ub.y + dc.x * uc.x + dc.y * uc.y);
+                    o[2] = mk2(da.x * ud.x + da.y * ud.y + db.x * ue.x, db.y * ud.x + dc.x * ud.y + dc.y * ue.x);
+                }
+                __syncwarp();
+            }
+            cur = nxt;
         }
     }
-    __syncthreads();
 
-    // ---- E: the Jacobian tile leaves as one bulk async copy; meanwhile warps reduce the cost terms ----------------
-    if (JAC && tid == 0) {
-        const uint32_t bytes = (uint32_t)(nv * C * jw * sizeof(T));
-        T *g = reinterpret_cast<T *>(p.eo.jac) + (size_t)f0 * C * jw;
-        const uint32_t saddr = (uint32_t)__cvta_generic_to_shared(stage);
-        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(g), "r"(saddr), "r"(bytes)
-                     : "memory");
-        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-    }
+    // ---- E: fixed-order warp reductions of the four cost terms ---------------------------------------------------------
     if (p.eo.frame_cost) {
-        const int wid = tid >> 5, lane = tid & 31, nw = blockDim.x >> 5;
-        for (int f = wid; f < nv; f += nw) {
-            const double *ctr = frd0 + f * p.fd + CTR;
-            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-            for (int i = lane; i < TPF; i += 32) a0 += ctr[MEC + i];
-            for (int i = lane; i < 54; i += 32) a1 += ctr[MOC + i];
-            if (lane < 26) a2 = ctr[EQC + lane];
-            if (lane < n_ineq) a3 = ctr[INC + lane];
-            a0 = warp_sum(a0); a1 = warp_sum(a1); a2 = warp_sum(a2); a3 = warp_sum(a3);
-            if (lane == 0) {
-                double *o = p.eo.frame_cost + (size_t)(f0 + f) * 4;
-                o[0] = a0; o[1] = a1; o[2] = a2; o[3] = a3;
-            }
+        const double a0 = warp_sum((double)rho), a1 = warp_sum(a_mo), a2 = warp_sum(a_eq), a3 = warp_sum(a_in);
+        if (lane == 0) {
+            double *o = p.eo.frame_cost + (size_t)fi * 4;
+            o[0] = a0; o[1] = a1; o[2] = a2; o[3] = a3;
         }
     }
-    if (JAC && tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
 
-template <typename T, bool JAC, int MAXT, int MINB>
-static int launch_cfg(const EvalParams &p, int grid, int threads, size_t smem, cudaStream_t st) {
-    cudaError_t e = cudaFuncSetAttribute(eval_kernel<T, JAC, MAXT, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+template <typename T, bool JAC, int WPC, int MINB>
+static int launch_cfg(const EvalParams &p, int grid, size_t smem, cudaStream_t st) {
+    cudaError_t e = cudaFuncSetAttribute(eval_kernel<T, JAC, WPC, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)smem);
     if (e != cudaSuccess) return (int)e;
-    eval_kernel<T, JAC, MAXT, MINB><<<grid, threads, smem, st>>>(p);
+    eval_kernel<T, JAC, WPC, MINB><<<grid, WPC * 32, smem, st>>>(p);
     return (int)cudaGetLastError();
 }
 
-static inline int up32(int x) { return (x + 31) & ~31; }
+static int eval_cfg() {
+    static int cfg = -1;
+    if (cfg < 0) {
+        const char *e = getenv("CPE_EVAL_CFG");      // tuning knob for experiments; default chosen by measurement
+        cfg = e ? atoi(e) : 0;
+    }
+    return cfg;
+}
 
 template <typename T>
 static int launch_eval(const cpe_model *model, const cpe_batch *b, const double *q, const cpe_eval_out *eo,
@@ -358,44 +333,38 @@ static int launch_eval(const cpe_model *model, const cpe_batch *b, const double 
     if (model->n_ineq > CPE_MAX_INEQ || model->n_u <= 0 || model->n_u > 240 || model->n_u % 3) return CPE_E_DIM;
     if (b->meas_layout < 0 || b->meas_layout > CPE_MEAS_F32X3) return CPE_E_ARG;
     if (!b->meas || !b->cams || !b->chain_vec || !b->n_frames || !b->h) return CPE_E_NULL;
-    const bool jac = eo->jac != nullptr;
     if (!model->u_off || !model->u_item) return CPE_E_NULL;
+    constexpr bool f64 = sizeof(T) == 8;
+    constexpr int WPC = 4;
+    const bool jac = eo->jac != nullptr;
     EvalParams p;
     p.m = *model; p.b = *b; p.q = q; p.eo = *eo;
     p.ea = exp(b->loss_a); p.eb = exp(b->loss_b); p.ec = exp(b->loss_c);
     p.TPF = b->C * 24;
-    int F = 160 / p.TPF;                                // frames packed into one 160-thread CTA
-    if (F < 1) F = 1;
-    if (F > 6) F = 6;
-    if (F > b->N) F = b->N;
-    p.F = F;
-    p.chunks = (b->N + F - 1) / F;
+    p.chunks = (b->N + WPC - 1) / WPC;
     p.n_u = model->n_u;
     p.n_pair = model->n_u / 3;
-    p.i_mk = up32(p.n_pair);
-    p.i_tc = p.i_mk + 32;
-    p.i_eq = p.i_tc + up32(3 * b->C);
-    p.i_in = p.i_eq + 32;
-    p.i_mo = p.i_in + up32(model->n_ineq > 0 ? model->n_ineq : 1);
-    p.i_end = p.i_mo + 64;
-    p.fd = (CTR + MEC + p.TPF + 1) & ~1;
-    p.ft = (T_U + 8 * p.n_pair + 3) & ~3;
-    const bool f64 = sizeof(T) == 8;
-    p.off_t = (int)sizeof(double) * (b->C * CPE_CAM_STRIDE + F * p.fd);
-    const size_t t_elems = (size_t)(f64 ? 0 : b->C * CPE_CAM_STRIDE) + (size_t)F * p.ft;
-    p.off_stage = (int)((p.off_t + t_elems * sizeof(T) + 15) & ~(size_t)15);
-    const size_t smem = (size_t)p.off_stage + (jac ? (size_t)F * b->C * 2 * (72 + p.n_u) * sizeof(T) : 0);
-    int threads = up32(F * p.TPF);
-    if (threads < 128) threads = 128;
+    p.nitem = 24 + p.n_pair;
+    p.item_magic = ((1u << 24) + p.nitem - 1) / p.nitem;
+    if (jac && !model->col_item) return CPE_E_NULL;
+    const int t_elems = (f64 ? 0 : 104) + T_U + 10 + 10 * p.n_pair;
+    p.wbytes = (int)((WD * sizeof(double) + t_elems * sizeof(T) + 15) & ~(size_t)15);
+    p.off_warp = (int)(b->C * CPE_CAM_STRIDE * (sizeof(double) + (f64 ? 0 : sizeof(T))) +
+                       sizeof(int32_t) * ((p.nitem + 3) & ~3));
+    const size_t smem = (size_t)p.off_warp + (size_t)WPC * p.wbytes;
     const long long grid_ll = (long long)b->S * p.chunks;
     if (grid_ll > 0x7fffffffLL) return CPE_E_DIM;
     const int grid = (int)grid_ll;
-    if (threads > 160)
-        return jac ? launch_cfg<T, true, 192, 4>(p, grid, threads, smem, st)
-                   : launch_cfg<T, false, 192, 4>(p, grid, threads, smem, st);
-    constexpr int MINB = sizeof(T) == 8 ? 6 : 8;
-    return jac ? launch_cfg<T, true, 160, MINB>(p, grid, threads, smem, st)
-               : launch_cfg<T, false, 160, MINB>(p, grid, threads, smem, st);
+    const int cfg = eval_cfg();
+    if constexpr (f64) {
+        if (cfg == 1) return jac ? launch_cfg<T, true, WPC, 6>(p, grid, smem, st) : launch_cfg<T, false, WPC, 6>(p, grid, smem, st);
+        if (cfg == 2) return jac ? launch_cfg<T, true, WPC, 5>(p, grid, smem, st) : launch_cfg<T, false, WPC, 5>(p, grid, smem, st);
+        return jac ? launch_cfg<T, true, WPC, 7>(p, grid, smem, st) : launch_cfg<T, false, WPC, 7>(p, grid, smem, st);
+    } else {
+        if (cfg == 1) return jac ? launch_cfg<T, true, WPC, 8>(p, grid, smem, st) : launch_cfg<T, false, WPC, 8>(p, grid, smem, st);
+        if (cfg == 2) return jac ? launch_cfg<T, true, WPC, 12>(p, grid, smem, st) : launch_cfg<T, false, WPC, 12>(p, grid, smem, st);
+        return jac ? launch_cfg<T, true, WPC, 10>(p, grid, smem, st) : launch_cfg<T, false, WPC, 10>(p, grid, smem, st);
+    }
 }
 
 }  // namespace cpe

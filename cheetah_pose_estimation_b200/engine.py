@@ -15,7 +15,7 @@ from . import _lib, skeleton
 FISHEYE, PINHOLE = 0, 1
 MEAS_F32X4, MEAS_F64X4, MEAS_F32X3 = 0, 1, 2      # include/cpe.h CPE_MEAS_*
 _I32_KEYS = ("chain_link", "eq_pairs", "ineq_idx", "ind_idx", "ind_pos", "grp_ndep", "grp_nnb", "grp_dep", "grp_nb",
-             "u_off", "u_item", "ent_pq", "a_ptr", "a_items", "e_ptr", "e_items", "i_ptr", "i_items", "diag_ent",
+             "u_off", "u_item", "col_item", "ent_pq", "a_ptr", "a_items", "e_ptr", "e_items", "i_ptr", "i_items", "diag_ent",
              "grad_ent", "grp_src", "s_src", "s_ptr", "s_items")
 _F64_KEYS = ("ineq_bounds", "wq", "meas_w")
 

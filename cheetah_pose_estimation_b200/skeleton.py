@@ -317,8 +317,17 @@ def build_tables(kinetic_dataset=False):
         for j, p in enumerate(nbs):
             grp_nbpos[g, ind_pos[p]] = j
     u_off, u_item, jac_cols = jacobian_pattern(chain_link)
+    # K1 Jacobian items of one frame.view in packed order; one item = 3 adjacent columns (the base x, y, z of a marker,
+    # or phi, theta, psi of one chain link): (marker << 16) | offset of the item's 3x3 block in the kernel's U array
+    # (10 values per block; block 0 = identity, block 1 + k = (marker, link) pair k in u_item order)
+    col_item = []
+    for l in range(N_MARKERS):
+        col_item.append((l << 16) | 0)
+        for k in range(int(u_off[l]) // 3, int(u_off[l + 1]) // 3):
+            col_item.append((l << 16) | (10 * (1 + k)))
+    col_item = np.array(col_item, np.int32)
     return dict(
-        u_off=u_off, u_item=u_item, n_u=len(u_item),
+        u_off=u_off, u_item=u_item, n_u=len(u_item), col_item=col_item,
         chain_link=chain_link.reshape(-1), slot_of=slot_of.reshape(-1), eq_pairs=eq.reshape(-1),
         ineq_idx=ineq_idx.reshape(-1), ineq_bounds=ineq_bounds.reshape(-1), wq=motion_weights(),
         meas_w=measurement_weights(kinetic_dataset).reshape(-1), ind_idx=ind, ind_pos=ind_pos,

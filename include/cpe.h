@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 103          /* 0.1.3 */
+#define CPE_VERSION 104          /* 0.1.4 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -85,6 +85,9 @@ typedef struct cpe_model {
     const int32_t *grp_nb;          /* [n_groups*12] coordinate indices (independent) */
     const int32_t *u_off;           /* [25] first packed chain column of marker l (prefix sum of 3*chainlen) */
     const int32_t *u_item;          /* [n_u] (marker << 8) | (chain slot << 4) | angle, per packed chain column */
+    const int32_t *col_item;        /* [24+n_u/3] K1 Jacobian items of one frame.view in packed order, one per 3 adjacent
+                                       columns (base x,y,z of a marker, or phi,theta,psi of a chain link):
+                                       (marker << 16) | 10 * block, block 0 = identity, 1 + k = (marker, link) pair k */
     /* static gather lists of K2 (skeleton.assemble_tables); entry e = Hessian nonzero (p >= q) or gradient p */
     const int32_t *ent_pq;          /* [n_ent] p*64 + q ; q = 63 marks a gradient entry */
     const int32_t *a_ptr;           /* [n_ent+1] marker items: (offset in G space << 16) | offset in B space */
