@@ -25,9 +25,12 @@
 //   C  rounds of warp-uniform items: chain derivative blocks U = dR/dangle . v (one item per (marker, link)),
 //      marker offsets, camera translations, joint equalities, inequalities, motion terms; the cost terms stay in
 //      lane registers
-//   D  rounds of 32 (camera, marker) pairs: projection, residuals, loss, Jacobian columns written straight from
-//      registers (the 32 marker blocks of a round are one contiguous span of the packed Jacobian; L2 merges the
-//      16-byte pieces into full lines before they reach HBM); the next round's detections are in flight meanwhile
+//   D  rounds of 32 (camera, marker) pairs.  Pair pass (lane <-> pair): projection, residuals, loss, and the 2x3
+//      projection derivative of each pair into shared memory; the next round's detections are in flight meanwhile.
+//      Item pass (lane <-> 3 adjacent Jacobian columns: base x,y,z of a marker or phi,theta,psi of a chain link):
+//      J = dproj(2x3) . block(3x3).  The 32 pairs of a round own ONE contiguous span of the packed Jacobian and
+//      consecutive lanes own consecutive 48-byte (24-byte in FP32) pieces of it, so the three stores of a round
+//      fill the span without gaps (per-pair stores from registers were LSU-wavefront bound: 32 lines per store)
 //   E  fixed-order shuffle reductions -> frame_cost
 // No atomics, no cross-warp reductions: a sequence's results are bit-identical whatever its batch neighbours are.
 #include <cuda_runtime.h>
@@ -60,8 +63,8 @@ struct EvalParams {
 constexpr int QO = 0, SCO = 56, RO = 160, WD = 314;
 // per-warp T slice (elements): marker offsets, camera translations, U = 3x3 blocks padded to 10 (block 0 = identity,
 // block 1 + k = dR/d(phi,theta,psi) . v of (marker, link) pair k); the f32 flavour also keeps a float copy of sin/cos
-// in front.  The d(u,v)/d(point) rows of the 32 pairs of
-// a round (6 T each) reuse the sin/cos + rotation doubles, which are dead after phase C.
+// in front.  The d(u,v)/d(point) rows of the 32 pairs of a round (6 T each) reuse the sin/cos + rotation doubles,
+// which are dead after phase C.
 constexpr int T_POS = 0, T_TC = 72, T_U = 96;
 
 template <typename T> struct Vec;
@@ -320,7 +323,7 @@ static int eval_cfg() {
     static int cfg = -1;
     if (cfg < 0) {
         const char *e = getenv("CPE_EVAL_CFG");      // tuning knob for experiments; default chosen by measurement
-        cfg = e ? atoi(e) : 0;
+        cfg = e ? atoi(e) : 1;      // 1: 6 CTAs/SM (80 regs) for FP64, 8 CTAs/SM (64 regs) for FP32
     }
     return cfg;
 }
@@ -357,13 +360,13 @@ static int launch_eval(const cpe_model *model, const cpe_batch *b, const double 
     const int grid = (int)grid_ll;
     const int cfg = eval_cfg();
     if constexpr (f64) {
-        if (cfg == 1) return jac ? launch_cfg<T, true, WPC, 6>(p, grid, smem, st) : launch_cfg<T, false, WPC, 6>(p, grid, smem, st);
+        if (cfg == 0) return jac ? launch_cfg<T, true, WPC, 7>(p, grid, smem, st) : launch_cfg<T, false, WPC, 7>(p, grid, smem, st);
         if (cfg == 2) return jac ? launch_cfg<T, true, WPC, 5>(p, grid, smem, st) : launch_cfg<T, false, WPC, 5>(p, grid, smem, st);
-        return jac ? launch_cfg<T, true, WPC, 7>(p, grid, smem, st) : launch_cfg<T, false, WPC, 7>(p, grid, smem, st);
+        return jac ? launch_cfg<T, true, WPC, 6>(p, grid, smem, st) : launch_cfg<T, false, WPC, 6>(p, grid, smem, st);
     } else {
-        if (cfg == 1) return jac ? launch_cfg<T, true, WPC, 8>(p, grid, smem, st) : launch_cfg<T, false, WPC, 8>(p, grid, smem, st);
+        if (cfg == 0) return jac ? launch_cfg<T, true, WPC, 10>(p, grid, smem, st) : launch_cfg<T, false, WPC, 10>(p, grid, smem, st);
         if (cfg == 2) return jac ? launch_cfg<T, true, WPC, 12>(p, grid, smem, st) : launch_cfg<T, false, WPC, 12>(p, grid, smem, st);
-        return jac ? launch_cfg<T, true, WPC, 10>(p, grid, smem, st) : launch_cfg<T, false, WPC, 10>(p, grid, smem, st);
+        return jac ? launch_cfg<T, true, WPC, 8>(p, grid, smem, st) : launch_cfg<T, false, WPC, 8>(p, grid, smem, st);
     }
 }
 
