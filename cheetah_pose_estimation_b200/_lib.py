@@ -52,6 +52,11 @@ class CpeAssembleOut(C.Structure):
                 ("Hraw", c_f64p)]
 
 
+class CpePrior(C.Structure):
+    _fields_ = [("n_comp", C.c_int32), ("window", C.c_int32), ("Tr", c_f64p), ("gmm_logc", c_f64p), ("gmm_mu", c_f64p),
+                ("gmm_prec", c_f64p), ("ar_W", c_f64p), ("ar_b", c_f64p), ("ar_wt", c_f64p)]
+
+
 class CpeSolveIO(C.Structure):
     _fields_ = [("Lfac", c_f64p), ("zbuf", c_f64p), ("delta_ind", c_f64p), ("status", c_i32p)]
 
@@ -69,6 +74,14 @@ EXPORTS = {
                                      C.POINTER(CpeAssembleOut), c_f64p, c_f64p, c_f64p, c_f64p, C.c_void_p]),
     "cpe_step_accept_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p, c_f64p, c_f64p, c_i32p, c_i32p,
                                       C.c_double, C.c_void_p]),
+    "cpe_step_accept_prior_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p, c_f64p, c_f64p, c_f64p, c_i32p,
+                                            c_i32p, C.c_double, C.c_void_p]),
+    "cpe_prior_cost_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpePrior), C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p,
+                                     C.c_void_p]),
+    "cpe_prior_assemble_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpePrior), C.POINTER(CpeBatch), c_f64p, c_f64p,
+                                         C.POINTER(CpeAssembleOut), C.c_void_p]),
+    "cpe_band_solve_general_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p, C.c_int64, C.c_int32, c_f64p,
+                                             c_f64p, c_i32p, C.c_void_p]),
     "cpe_update_multipliers_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p,
                                              c_f64p, C.c_void_p]),
     "cpe_eval_host_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpeBatch), C.c_void_p, C.c_void_p, c_f64p,

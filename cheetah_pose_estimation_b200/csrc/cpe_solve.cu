@@ -92,7 +92,7 @@ __global__ void reduce_cost_kernel(int S, int N, const int32_t *n_frames, const 
 
 // ---- K5: accept / reject ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) step_accept_kernel(int S, int N, const int32_t *n_frames, const double *cost_try,
-                                                          const double *frame_pred, double *q, const double *q_try,
+                                                          const double *cost_extra, const double *frame_pred, double *q, const double *q_try,
                                                           double *state, int32_t *counters, int32_t *active, double ftol) {
     const int s = blockIdx.x;
     __shared__ int accept;
@@ -105,7 +105,8 @@ __global__ void __launch_bounds__(128) step_accept_kernel(int S, int N, const in
         for (int o = 16; o > 0; o >>= 1) pred += __shfl_down_sync(0xffffffffu, pred, o);
         if (threadIdx.x == 0) {
             const double *ct = cost_try + (size_t)s * 4;
-            const double Ft = ct[0] + ct[1] + ct[2] + ct[3];
+            double Ft = ct[0] + ct[1] + ct[2] + ct[3];
+            if (cost_extra) Ft += cost_extra[(size_t)s * 2] + cost_extra[(size_t)s * 2 + 1];   // monocular priors
             double F = state[s], damp = state[S + s], nu = state[2 * S + s];
             int acc = 0;
             double rel = -1.0;
@@ -175,8 +176,17 @@ extern "C" int cpe_step_accept_f64(const cpe_batch *b, const double *cost_try, c
                                    const double *q_try, double *state, int32_t *counters, int32_t *active,
                                    double ftol, void *stream) {
     if (!b || !cost_try || !frame_pred || !q || !q_try || !state || !counters) return CPE_E_NULL;
-    cpe::step_accept_kernel<<<b->S, 128, 0, (cudaStream_t)stream>>>(b->S, b->N, b->n_frames, cost_try, frame_pred, q, q_try,
-                                                                    state, counters, active, ftol);
+    cpe::step_accept_kernel<<<b->S, 128, 0, (cudaStream_t)stream>>>(b->S, b->N, b->n_frames, cost_try, nullptr, frame_pred,
+                                                                    q, q_try, state, counters, active, ftol);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int cpe_step_accept_prior_f64(const cpe_batch *b, const double *cost_try, const double *cost_extra,
+                                         const double *frame_pred, double *q, const double *q_try, double *state,
+                                         int32_t *counters, int32_t *active, double ftol, void *stream) {
+    if (!b || !cost_try || !cost_extra || !frame_pred || !q || !q_try || !state || !counters) return CPE_E_NULL;
+    cpe::step_accept_kernel<<<b->S, 128, 0, (cudaStream_t)stream>>>(b->S, b->N, b->n_frames, cost_try, cost_extra,
+                                                                    frame_pred, q, q_try, state, counters, active, ftol);
     return (int)cudaGetLastError();
 }
 

@@ -150,14 +150,30 @@ class Batch:
 class Solver:
     """Workspaces + launches for one (model, batch)."""
 
-    def __init__(self, model: Model, batch: Batch, with_solver=True):
+    def __init__(self, model: Model, batch: Batch, with_solver=True, priors=None):
+        """priors: a `priors.Priors` (monocular data-driven terms) or None."""
         self.m, self.b = model, batch
         self.lib = model.lib
+        self.priors = priors
         S, N, dev = batch.S, batch.N, model.device
         f64 = dict(dtype=torch.float64, device=dev)
         self.frame_cost = torch.zeros(S, N, 4, **f64)
         self.cost = torch.zeros(S, 4, **f64)
         self.launches = 0
+        if priors is not None:
+            self.prior_frame = torch.zeros(S, N, 2, **f64)
+            self.prior_cost = torch.zeros(S, 2, **f64)
+            if with_solver:
+                # constant band of the motion terms, one per sequence (depends on n_frames and h)
+                nfs, hs = batch.n_frames.cpu().numpy(), batch.h.cpu().numpy()
+                cache, rows = {}, []
+                for nf, h in zip(nfs, hs):
+                    key = (int(nf), float(h))
+                    if key not in cache:
+                        cache[key] = priors.mband(int(nf), float(h), N)
+                    rows.append(cache[key])
+                self.Mband = torch.as_tensor(np.stack(rows), device=dev)
+                self.Lband = torch.empty(S, N * 28, priors.bw + 1, **f64)
         if with_solver:
             G = model.n_groups
             self.Sblk = torch.zeros(S, N, 28, 28, **f64)
@@ -180,7 +196,8 @@ class Solver:
             self.v_in = torch.zeros(S, N, model.n_ineq, **f64)
 
     # ---- K1 --------------------------------------------------------------------------------------------------
-    def evaluate(self, q, pose=False, resid=False, constraints=False, jac=False, cost_out=None, buffers=None, f32=False):
+    def evaluate(self, q, pose=False, resid=False, constraints=False, jac=False, cost_out=None, buffers=None, f32=False,
+                 prior_out=None):
         """cost[S,4] = (measurement, model, al_eq, al_in) and optional per-frame outputs.  `buffers` may hold
         preallocated output tensors ("pose", "resid", "jac") to write into instead of allocating.  f32=True runs the
         scaled FP32 flavour (cpe_eval_f32): resid / jac come back as float32."""
@@ -215,7 +232,18 @@ class Solver:
         _lib.check(self.lib.cpe_reduce_cost_f64(C.byref(bs), _ptr(self.frame_cost), _ptr(cost), st), "cpe_reduce_cost_f64")
         self.launches += 2
         out["cost"] = cost
+        if self.priors is not None:
+            out["prior_cost"] = self.evaluate_priors(q, prior_out)
         return out
+
+    def evaluate_priors(self, q, prior_out=None):
+        """prior_cost[S,2] = (pose, motion) of the monocular priors at q."""
+        pc = self.prior_cost if prior_out is None else prior_out
+        bs = self.b.struct()
+        _lib.check(self.lib.cpe_prior_cost_f64(C.byref(self.m.struct), C.byref(self.priors.struct), C.byref(bs), _ptr(q),
+                                               _ptr(self.prior_frame), _ptr(pc), _stream()), "cpe_prior_cost_f64")
+        self.launches += 2
+        return pc
 
     def evaluate_launch(self, q, buffers, cost_out, record_mid=None):
         """Lean K1 launch for wave loops: residuals + chain-sparse Jacobian into preallocated `buffers`
@@ -258,10 +286,23 @@ class Solver:
         _lib.check(self.lib.cpe_assemble_f64(C.byref(self.m.struct), C.byref(bs), _ptr(q), _ptr(damp), C.byref(ao), _stream()),
                    "cpe_assemble_f64")
         self.launches += 1
+        if self.priors is not None and reduced:
+            _lib.check(self.lib.cpe_prior_assemble_f64(C.byref(self.m.struct), C.byref(self.priors.struct), C.byref(bs),
+                                                       _ptr(q), _ptr(damp), C.byref(ao), _stream()),
+                       "cpe_prior_assemble_f64")
+            self.launches += 1
         return Hraw
 
     # ---- K3 --------------------------------------------------------------------------------------------------
     def band_solve(self):
+        if self.priors is not None:
+            bs = self.b.struct()
+            _lib.check(self.lib.cpe_band_solve_general_f64(
+                C.byref(bs), _ptr(self.Sblk), _ptr(self.ghat), _ptr(self.Mband), C.c_int64(self.Mband.stride(0)),
+                C.c_int32(self.priors.bw), _ptr(self.Lband), _ptr(self.delta_ind), _ptr(self.status), _stream()),
+                "cpe_band_solve_general_f64")
+            self.launches += 1
+            return self.delta_ind
         io = _lib.CpeSolveIO()
         io.Lfac, io.zbuf, io.delta_ind, io.status = (self.Lfac.data_ptr(), self.zbuf.data_ptr(), self.delta_ind.data_ptr(),
                                                      self.status.data_ptr())
@@ -303,20 +344,30 @@ class Solver:
         self.state[2].fill_(2.0)
         self.counters.zero_()
         cost_try = torch.zeros(S, 4, dtype=torch.float64, device=dev)
+        prior_try = torch.zeros(S, 2, dtype=torch.float64, device=dev) if self.priors is not None else None
         damp = self.state[1]
         total_inner = 0
         for outer in range(n_outer):
             b.mu_eq = b.mu_in = float(mu_schedule[min(outer, len(mu_schedule) - 1)])
             self.evaluate(q)
             self.state[0].copy_(self.cost.sum(dim=1))
+            if self.priors is not None:
+                self.state[0].add_(self.prior_cost.sum(dim=1))
             self.active.fill_(1)
             for it in range(max_iter):
                 self.lm_step(q, damp)
-                self.evaluate(self.q_try, cost_out=cost_try)
+                self.evaluate(self.q_try, cost_out=cost_try, prior_out=prior_try)
                 bs = b.struct()
-                _lib.check(lib.cpe_step_accept_f64(C.byref(bs), _ptr(cost_try), _ptr(self.frame_pred), _ptr(q),
-                                                   _ptr(self.q_try), _ptr(self.state), _ptr(self.counters),
-                                                   _ptr(self.active), C.c_double(ftol), _stream()), "cpe_step_accept_f64")
+                if self.priors is not None:
+                    _lib.check(lib.cpe_step_accept_prior_f64(C.byref(bs), _ptr(cost_try), _ptr(prior_try),
+                                                             _ptr(self.frame_pred), _ptr(q), _ptr(self.q_try),
+                                                             _ptr(self.state), _ptr(self.counters), _ptr(self.active),
+                                                             C.c_double(ftol), _stream()), "cpe_step_accept_prior_f64")
+                else:
+                    _lib.check(lib.cpe_step_accept_f64(C.byref(bs), _ptr(cost_try), _ptr(self.frame_pred), _ptr(q),
+                                                       _ptr(self.q_try), _ptr(self.state), _ptr(self.counters),
+                                                       _ptr(self.active), C.c_double(ftol), _stream()),
+                               "cpe_step_accept_f64")
                 self.launches += 1
                 total_inner += 1
                 if (it + 1) % check_every == 0 and not bool(self.active.any()):
@@ -328,8 +379,11 @@ class Solver:
                        "cpe_update_multipliers_f64")
             self.launches += 1
         out = self.evaluate(q, constraints=True)
-        return dict(q=q, cost=out["cost"].clone(), c_eq=out["c_eq"], v_in=out["v_in"], counters=self.counters.clone(),
-                    status=self.status.clone(), lockstep_iterations=total_inner)
+        res = dict(q=q, cost=out["cost"].clone(), c_eq=out["c_eq"], v_in=out["v_in"], counters=self.counters.clone(),
+                   status=self.status.clone(), lockstep_iterations=total_inner)
+        if self.priors is not None:
+            res["prior_cost"] = out["prior_cost"].clone()
+        return res
 
 
 class HostEvaluator:

@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 104          /* 0.1.4 */
+#define CPE_VERSION 105          /* 0.1.5 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -155,6 +155,27 @@ typedef struct cpe_assemble_out {
     double *Hraw;                   /* optional [S,N,54,54] dense undamped frame Hessian (tests / cpe_normal_eq) */
 } cpe_assemble_out;
 
+/* Data-driven monocular priors on the reduced pose x = Tr q_ind (28 = the coordinates with a motion prior; the
+ * reduced pose only involves those: acinoset_misc.py:487-528, 1699-1757).  Parameters are fitted on the CPU as in the
+ * reference (acinoset_models.py:173-300) and frozen here; the kernels evaluate
+ *   pose   sum_frames -log( sum_c exp(logc_c - 1/2 d_c^T P_c d_c) + 1e-12 ),  d_c = x[6:28] - mu_c   (acinoset_misc.py:680-714)
+ *   motion sum_{k >= window} sum_p wt_p ( x_k - W [x_{k-window}; ...; x_{k-1}] - b )_p^2              (acinoset_misc.py:291-336)
+ * with logc_c = log w_c - 1/2 (22 log 2 pi + log det Sigma_c), P_c = Sigma_c^-1. */
+#define CPE_PRIOR_MAX_COMP 8
+#define CPE_PRIOR_MAX_WINDOW 4
+#define CPE_PRIOR_DIM 22          /* entries 6..27 of the reduced pose */
+typedef struct cpe_prior {
+    int32_t n_comp;                 /* GMM components (0 = pose prior off) */
+    int32_t window;                 /* AR window (0 = motion prior off; <= CPE_PRIOR_MAX_WINDOW) */
+    const double *Tr;               /* [28*28] x = Tr q_ind */
+    const double *gmm_logc;         /* [n_comp] */
+    const double *gmm_mu;           /* [n_comp*22] */
+    const double *gmm_prec;         /* [n_comp*22*22] */
+    const double *ar_W;             /* [28*(28*window)] oldest lag first (data_ops.py:108-142) */
+    const double *ar_b;             /* [28] */
+    const double *ar_wt;            /* [28] 1/var_p, 0 where var_p = 0 (acinoset_misc.py:308) */
+} cpe_prior;
+
 /* Workspace + outputs of the block-banded solve. */
 typedef struct cpe_solve_io {
     double *Lfac;                   /* [S,N,3,28,28] workspace: L1, L2, L3 (unit-lower block factors of each block row) */
@@ -200,6 +221,30 @@ int cpe_step_apply_f64(const cpe_model *model, const cpe_batch *batch, const dou
 int cpe_step_accept_f64(const cpe_batch *batch, const double *cost_try, const double *frame_pred, double *q,
                         const double *q_try, double *state, int32_t *counters, int32_t *active, double ftol,
                         void *stream);
+/* Same, with the prior costs of the trial point added to the merit: cost_extra[S,2] = (pose, motion). */
+int cpe_step_accept_prior_f64(const cpe_batch *batch, const double *cost_try, const double *cost_extra,
+                              const double *frame_pred, double *q, const double *q_try, double *state,
+                              int32_t *counters, int32_t *active, double ftol, void *stream);
+
+/* Monocular priors, cost only: prior_cost[S,2] = (pose, motion) of q[S,N,54]; frame_work[S,N,2] is scratch. */
+int cpe_prior_cost_f64(const cpe_model *model, const cpe_prior *prior, const cpe_batch *batch, const double *q,
+                       double *frame_work, double *prior_cost, void *stream);
+
+/* Monocular priors, normal-equation side: call AFTER cpe_assemble_f64 on the same q / damp.  Adds, per frame, the
+ * gradient of both priors to out->ghat and out->g, and the PSD majoriser sum_c r_c Tr^T P_c Tr of the pose-prior
+ * Hessian to out->S (plus damp * its diagonal) and its diagonal to out->diagH.  The motion prior's exact (constant)
+ * Hessian 2 J^T W J is not added here: it is part of the band `Mband` given to cpe_band_solve_general_f64. */
+int cpe_prior_assemble_f64(const cpe_model *model, const cpe_prior *prior, const cpe_batch *batch, const double *q,
+                           const double *damp, const cpe_assemble_out *out, void *stream);
+
+/* General banded SPD solve of (blockdiag(S) + M) d = -ghat per sequence, n = 28 N unknowns, scalar half-bandwidth
+ * bw (<= 139 = 28 * 5 - 1: AR window 4).  Mband[n][bw+1] holds the lower band of the constant part M (motion terms):
+ * Mband[i][d] = M(i, i-d); sequence s reads Mband + s * mband_stride (0 = shared by all sequences).  Lband[S][n][bw+1]
+ * is workspace (the Cholesky factor, column-major band).  Used by the monocular path, whose AR(4) prior couples five
+ * consecutive frames with dense 28x28 blocks; the multi-view path keeps cpe_band_solve_f64. */
+int cpe_band_solve_general_f64(const cpe_batch *batch, const double *Sblk, const double *ghat, const double *Mband,
+                               int64_t mband_stride, int32_t bw, double *Lband, double *delta_ind, int32_t *status,
+                               void *stream);
 
 /* Augmented-Lagrangian multiplier update: lam_eq += mu_eq * c_eq ; lam_in = mu_in * v_in. */
 int cpe_update_multipliers_f64(const cpe_model *model, const cpe_batch *batch, const double *c_eq,

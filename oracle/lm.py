@@ -17,7 +17,7 @@ One LM step, per sequence:
 """
 import numpy as np
 
-from . import cost, tables
+from . import cost, priors as opriors, tables
 
 
 def split_indices():
@@ -26,8 +26,12 @@ def split_indices():
     return ind, dep
 
 
-def merit(pb, q, lam_eq, lam_in):
-    return float(cost.cost_terms(pb, q, lam_eq, lam_in).sum())
+def merit(pb, q, lam_eq, lam_in, pr=None):
+    """Sum of the cost terms; with `pr` (monocular priors, oracle.priors) the pose and motion priors are added."""
+    f = float(cost.cost_terms(pb, q, lam_eq, lam_in).sum())
+    if pr is not None:
+        f += float(opriors.prior_costs(pr, q).sum())
+    return f
 
 
 def schur_frames(H, g, diagH, damp):
@@ -93,18 +97,48 @@ def band_solve(S, ghat, m, wd_i):
     return d
 
 
-def lm_step(pb, q, lam_eq, lam_in, damp):
-    """Returns (delta[N,54], predicted_reduction, g[N,54])."""
+def dense_band_solve(S, ghat, m, wd_i, H_extra):
+    """(blockdiag(S) + const-acc band + H_extra) d = -ghat by a dense solve (monocular path: H_extra = AR Hessian)."""
+    N, n = S.shape[0], S.shape[1]
+    A = np.array(H_extra, dtype=float).copy()
+    for k in range(N):
+        A[k * n:(k + 1) * n, k * n:(k + 1) * n] += S[k]
+        for j in range(0, 4):
+            if k - j >= 0:
+                blk = m[k, j] * np.diag(wd_i)
+                A[k * n:(k + 1) * n, (k - j) * n:(k - j + 1) * n] += blk
+                if j > 0:
+                    A[(k - j) * n:(k - j + 1) * n, k * n:(k + 1) * n] += blk
+    return np.linalg.solve(A, -ghat.reshape(-1)).reshape(N, n)
+
+
+def lm_step(pb, q, lam_eq, lam_in, damp, pr=None):
+    """Returns (delta[N,54], predicted_reduction, g[N,54]).  With `pr` the monocular priors enter: gradients of both,
+    the PSD majoriser of the pose prior per frame (damped like the rest), the exact AR Hessian in the band."""
     ind, dep = split_indices()
     N = q.shape[0]
     H, g = cost.frame_normal_equations(pb, q, lam_eq, lam_in)
     g = g + cost.motion_gradient(pb, q)
+    H_ar = None
+    if pr is not None:
+        if "gmm_w" in pr:
+            gp, Hp = opriors.pose_grad_hess(pr, q)
+            H = H + Hp
+            g = g + gp
+        if "ar_W" in pr:
+            gm, Hm = opriors.motion_grad_hess(pr, q)
+            g = g + gm.reshape(N, 54)
+            sel = (np.arange(N)[:, None] * 54 + ind[None, :]).reshape(-1)
+            H_ar = Hm[np.ix_(sel, sel)]
     m = cost.motion_stencil(N)
     wd = 2.0 * pb.wq / pb.h ** 4
     idx = np.arange(54)
     diagH = H[:, idx, idx] + m[:, 0:1] * wd[None, :]
     S, ghat, Y, y = schur_frames(H, g, diagH, damp)
-    d_i = band_solve(S, ghat, m, wd[ind])
+    if pr is not None:
+        d_i = dense_band_solve(S, ghat, m, wd[ind], H_ar if H_ar is not None else np.zeros((N * 28, N * 28)))
+    else:
+        d_i = band_solve(S, ghat, m, wd[ind])
     delta = np.zeros((N, 54))
     delta[:, ind] = d_i
     delta[:, dep] = -(y + np.einsum("nab,nb->na", Y, d_i))
@@ -117,7 +151,8 @@ def update_multipliers(pb, q, lam_eq, lam_in):
     return lam_eq + pb.mu_eq * c, pb.mu_in * v
 
 
-def solve(pb, q0, max_iter=60, n_outer=4, damp0=1e-3, ftol=1e-6, mu_schedule=(1e4, 1e5, 1e6, 1e6), verbose=False):
+def solve(pb, q0, max_iter=60, n_outer=4, damp0=1e-3, ftol=1e-6, mu_schedule=(1e4, 1e5, 1e6, 1e6), verbose=False,
+          pr=None):
     """Returns dict(q, cost_terms, iters, accepted, history).  `mu_schedule[o]` is the AL penalty of outer
     iteration o (continuation: a soft penalty far from the optimum, stiff once the multipliers are good)."""
     N = q0.shape[0]
@@ -129,12 +164,12 @@ def solve(pb, q0, max_iter=60, n_outer=4, damp0=1e-3, ftol=1e-6, mu_schedule=(1e
     iters = accepted = 0
     for outer in range(n_outer):
         pb.mu_eq = pb.mu_in = float(mu_schedule[min(outer, len(mu_schedule) - 1)])
-        F = merit(pb, q, lam_eq, lam_in)
+        F = merit(pb, q, lam_eq, lam_in, pr)
         stall = 0
         for it in range(max_iter):
-            delta, pred, _ = lm_step(pb, q, lam_eq, lam_in, damp)
+            delta, pred, _ = lm_step(pb, q, lam_eq, lam_in, damp, pr)
             q_try = q + delta
-            F_try = merit(pb, q_try, lam_eq, lam_in)
+            F_try = merit(pb, q_try, lam_eq, lam_in, pr)
             iters += 1
             if np.isfinite(F_try) and F_try < F:
                 rho = (F - F_try) / max(pred, 1e-300)
@@ -158,5 +193,8 @@ def solve(pb, q0, max_iter=60, n_outer=4, damp0=1e-3, ftol=1e-6, mu_schedule=(1e
                 if damp >= 1e12:
                     break
         lam_eq, lam_in = update_multipliers(pb, q, lam_eq, lam_in)
-    return dict(q=q, cost_terms=cost.cost_terms(pb, q, lam_eq * 0, lam_in * 0), lam_eq=lam_eq, lam_in=lam_in,
-                iters=iters, accepted=accepted, history=hist)
+    out = dict(q=q, cost_terms=cost.cost_terms(pb, q, lam_eq * 0, lam_in * 0), lam_eq=lam_eq, lam_in=lam_in,
+               iters=iters, accepted=accepted, history=hist)
+    if pr is not None:
+        out["prior_costs"] = opriors.prior_costs(pr, q)
+    return out

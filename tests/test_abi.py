@@ -24,14 +24,14 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), n
     assert sorted(_lib.EXPORTS) == names
-    assert lib.cpe_version() == 104
+    assert lib.cpe_version() == 105
 
 
 def test_struct_mirrors_match_header_field_order():
     from cheetah_pose_estimation_b200 import _lib
     src = open(os.path.join(ROOT, "include", "cpe.h")).read()
     for cname, cls in (("cpe_model", _lib.CpeModel), ("cpe_batch", _lib.CpeBatch), ("cpe_eval_out", _lib.CpeEvalOut), ("cpe_eval_out_f32", _lib.CpeEvalOutF32),
-                       ("cpe_assemble_out", _lib.CpeAssembleOut), ("cpe_solve_io", _lib.CpeSolveIO)):
+                       ("cpe_assemble_out", _lib.CpeAssembleOut), ("cpe_solve_io", _lib.CpeSolveIO), ("cpe_prior", _lib.CpePrior)):
         body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (cname, cname), src, flags=re.S).group(1)
         fields = []
         for line in body.splitlines():
