@@ -194,15 +194,28 @@ def estimate_kinematics(estimator: CheetahEstimator,
                         motion_model_sparse_solution: bool = True,
                         out_dir_prefix: Optional[str] = None,
                         max_iter: int = 40,
-                        n_outer: int = 4) -> bool:
+                        n_outer: int = 4,
+                        models_dir: Optional[str] = None) -> bool:
     """Same arguments and side effects as the reference (acinoset_opt.py:539-635): initial guess from the spline
-    track, optimisation, COM, acceptance test, `save` into `fte_kinematic[_orig][_<cam>]`."""
+    track, optimisation, COM, acceptance test, `save` into `fte_kinematic[_orig][_<cam>]`.  With
+    `monocular_constraints` on a single-camera scene the GMM pose prior and the linear motion model are fitted on the
+    CPU from `<models_dir or ./models/data-driven>/dataset_full_pose.h5` (its `.csv` twin when PyTables is absent), as
+    the reference does (acinoset_misc.py:294-302, 684-689), and evaluated on the GPU inside the LM loop."""
     import torch
-    from . import engine
+    from . import acinoset_models, engine
+    from .priors import Priors
     params, scene = estimator.params, estimator.scene
+    priors = None
+    estimator.pose_model = estimator.motion_model = None
     if monocular_constraints and scene.cam_idx is not None and not (disable_pose_prior and disable_motion_prior):
-        raise NotImplementedError("data-driven monocular priors (GMM pose + linear motion model) are the next row of "
-                                  "the build (SURVEY.md section 8f.1); call with monocular_constraints=False")
+        ds = os.path.join(models_dir or os.path.join(".", "models", "data-driven"), "dataset_full_pose.h5")
+        if not disable_pose_prior:
+            estimator.pose_model = acinoset_models.PoseModelGMM(ds, num_vars=28, ext_dim=6,
+                                                                n_comps=pose_model_num_components)
+        if not disable_motion_prior:
+            estimator.motion_model = acinoset_models.MotionModel(ds, 28, window_size=motion_model_window_size,
+                                                                 window_time=1, lasso=motion_model_sparse_solution)
+        priors = Priors(acinoset_models.pack_priors(estimator.pose_model, estimator.motion_model), estimator.model.device)
     N = params.end_frame - params.start_frame
     x_est, y_est, z_est, psi_est = misc.create_trajectory_estimate(estimator.lengths[sk.BASE], params, scene,
                                                                    params.kinetic_dataset, estimator.base_data)
@@ -215,7 +228,7 @@ def estimate_kinematics(estimator: CheetahEstimator,
     batch = engine.Batch.from_numpy(estimator.meas[None], estimator.packed_cameras()[None], chain_vec[None],
                                     [1.0 / scene.fps], device=dev,
                                     cam_model=engine.PINHOLE if params.kinetic_dataset else engine.FISHEYE)
-    solver = engine.Solver(estimator.model, batch)
+    solver = engine.Solver(estimator.model, batch, priors=priors)
     time0 = time()
     res = solver.solve(torch.as_tensor(q0[None], device=dev), max_iter=max_iter, n_outer=n_outer)
     torch.cuda.synchronize()
@@ -236,7 +249,9 @@ def estimate_kinematics(estimator: CheetahEstimator,
     estimator.positions = out["pose"][0].cpu().numpy()
     estimator.meas_err = np.transpose(out["resid"][0].cpu().numpy(), (0, 1, 2, 4, 3))      # [N,C,24,2,W]
     cost = res["cost"][0].cpu().numpy()
-    estimator.costs = {"measurement": float(cost[0]), "model": float(cost[1]), "pose": 0.0, "motion": 0.0}
+    pc = res["prior_cost"][0].cpu().numpy() if priors is not None else np.zeros(2)
+    estimator.costs = {"measurement": float(cost[0]), "model": float(cost[1]), "pose": float(pc[0]),
+                       "motion": float(pc[1])}
     estimator.result = dict(status=int(res["status"][0]), cost=cost, c_eq=res["c_eq"][0].cpu().numpy(),
                             v_in=res["v_in"][0].cpu().numpy(), counters=res["counters"][0].cpu().numpy())
     if solver_output:

@@ -54,3 +54,48 @@ def test_kinematic_reconstruction_of_a_real_clip(golden_dir, tmp_path, animal, f
           f"obj_cost {float(g['obj_cost']):.3f} with the lost mask), MPJPE {mpjpe:.1f} mm, MPE {mpe:.1f} mm, "
           f"{d['processing_time_s']:.3f} s vs IPOPT {float(g['processing_time_s']):.1f} s")
     assert mpjpe < 30.0 and mpe < 60.0
+
+
+def _write_data_driven_dataset(golden_dir, models_dir):
+    """A stand-in for the reference's models/data-driven/dataset_full_pose.csv (which does not travel to the GPU box):
+    the reduced poses `x` of the reference's shipped trajectories (tests/golden/shipped_clips.npz), one segment per
+    clip, index restarting at 0 -- the same table layout (28 pose columns, 28 derivative columns)."""
+    import pandas as pd
+    g = np.load(os.path.join(golden_dir, "shipped_clips.npz"))
+    rows, idx = [], []
+    for key in sorted((k for k in g.keys() if k.endswith("_x")), key=lambda k: int(k.split("_")[0])):
+        x = g[key]
+        if x.shape[0] < 9:
+            continue
+        rows.append(np.concatenate([x, np.gradient(x, axis=0)], axis=1))
+        idx.append(np.arange(x.shape[0]))
+    os.makedirs(models_dir, exist_ok=True)
+    pd.DataFrame(np.concatenate(rows), index=np.concatenate(idx)).to_csv(os.path.join(models_dir, "dataset_full_pose.csv"))
+
+
+def test_monocular_reconstruction_with_data_driven_priors(golden_dir, tmp_path):
+    """BASELINE config 3 through the mirrored API: single camera, GMM pose prior + AR(4) motion model fitted on the
+    CPU (scikit-learn, as the reference), evaluated on the GPU inside the LM loop; output goes to fte_kinematic_<cam>."""
+    from cheetah_pose_estimation_b200 import acinoset_misc as misc, acinoset_opt as opt
+    path = "2017_08_29/top/jules/run1_1"
+    g = np.load(os.path.join(golden_dir, "clip_jules_run1_1.npz"))
+    root = str(tmp_path)
+    build_clip_dir(root, path, g)
+    models_dir = os.path.join(root, "models", "data-driven")
+    _write_data_driven_dataset(golden_dir, models_dir)
+    est = opt.init_trajectory(root, path, "jules", kinetic_dataset=False, solver_path="ignored", kinematic_model=True,
+                              monocular_enable=True)
+    assert est.scene.cam_idx == 0 and est.meas.shape[1] == 1
+    ok = opt.estimate_kinematics(est, solver_output=True, monocular_constraints=True, models_dir=models_dir)
+    assert ok
+    assert est.pose_model is not None and est.motion_model is not None
+    out_dir = os.path.join(root, path, "fte_kinematic_0")
+    d = pickle.load(open(os.path.join(out_dir, "fte.pickle"), "rb"))
+    N = g["detections"].shape[0]
+    assert d["q"].shape == (N, 54) and d["meas_err"].shape == (N, 1, 24, 2, 1)
+    assert np.isfinite(d["obj_cost"]) and est.costs["motion"] > 0 and np.isfinite(est.costs["pose"])
+    assert abs(d["obj_cost"] - 1e-3 * sum(est.costs.values())) < 1e-9
+    mpjpe = misc.traj_error(d["positions"].copy(), g["positions"].copy(), centered=True).mean()
+    print(f"monocular cam 0: obj {d['obj_cost']:.3f}, costs {est.costs}, MPJPE vs the shipped multi-view trajectory "
+          f"{mpjpe:.1f} mm, {d['processing_time_s']:.3f} s")
+    assert mpjpe < 250.0
