@@ -46,7 +46,7 @@ def parse_args():
     ap.add_argument("--frames", type=int, default=500)
     ap.add_argument("--cams", type=int, default=6)
     ap.add_argument("--wave", type=int, default=512, help="sequences per launch (Jacobian buffer reuse)")
-    ap.add_argument("--lm-seqs", type=int, default=296, help="sequences of the LM-solve leg (0 = skip)")
+    ap.add_argument("--lm-seqs", type=int, default=444, help="sequences of the LM-solve leg (0 = skip)")
     ap.add_argument("--lm-iters", type=int, default=20)
     ap.add_argument("--cpu-seqs", type=int, default=64, help="sequences of the cpu_baseline sample (0 = skip)")
     ap.add_argument("--no-e2e", action="store_true")

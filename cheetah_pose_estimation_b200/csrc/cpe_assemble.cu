@@ -57,7 +57,7 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
     const int N = p.b.N, C = p.b.C, W = p.b.W, TPF = p.TPF;
     const int s = blockIdx.y, k = blockIdx.x;
     const int nf = p.b.n_frames[s];
-    if (k >= nf) return;
+    if (k >= nf || (p.b.active && !p.b.active[s])) return;
     const size_t fidx = (size_t)s * N + k;
     const int n_ineq = p.m.n_ineq, n_u = p.m.n_u, n_ent = p.m.n_ent;
     double *cam = sm;

@@ -126,6 +126,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS, 3) band_solve_kernel(const __gr
     const int s = blockIdx.x;
     const int N = p.b.N;
     const int nf = p.b.n_frames[s];
+    if (p.b.active && !p.b.active[s]) return;
     double *colp = sm + 10 * BLK;        // [32][4]  pivot column panel (rows private to each warp)
     double *rowp = colp + 128;           // [4][32]  pivot row panel (owner warp only)
     double *Rp = rowp + 128;             // [2][4][32] scaled pivot rows, ping-pong

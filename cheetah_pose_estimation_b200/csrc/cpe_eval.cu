@@ -102,6 +102,7 @@ __global__ void __launch_bounds__(WPC * 32, MINB) eval_kernel(const __grid_const
     const int N = p.b.N, C = p.b.C, W = p.b.W, TPF = p.TPF;
     const int s = blockIdx.x / p.chunks;
     const int k = (blockIdx.x - s * p.chunks) * WPC + warp;
+    if (p.b.active && !p.b.active[s]) return;              // converged sequence of an LM loop (uniform per CTA)
     double *camd = reinterpret_cast<double *>(smraw);      // [C*24] FP64 camera rows
     T *camt = F64 ? reinterpret_cast<T *>(camd) : reinterpret_cast<T *>(smraw + sizeof(double) * C * CPE_CAM_STRIDE);
     int32_t *coltab = reinterpret_cast<int32_t *>(smraw + p.off_warp) - ((p.nitem + 3) & ~3);   // [nitem] Jacobian items

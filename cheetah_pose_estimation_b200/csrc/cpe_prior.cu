@@ -48,7 +48,7 @@ __global__ void __launch_bounds__(128) prior_kernel(const __grid_constant__ Prio
     const int N = p.b.N;
     const int s = blockIdx.y, k = blockIdx.x;
     const int nf = p.b.n_frames[s];
-    if (k >= nf) return;
+    if (k >= nf || (p.b.active && !p.b.active[s])) return;
     const int win = p.pr.window, ncomp = p.pr.n_comp;
     const size_t fidx = (size_t)s * N + k;
     const int nfr = 2 * win + 1;
@@ -191,10 +191,11 @@ __global__ void __launch_bounds__(128) prior_kernel(const __grid_constant__ Prio
     }
 }
 
-__global__ void reduce_prior_cost_kernel(int S, int N, const int32_t *n_frames, const double *frame_cost, double *cost) {
+__global__ void reduce_prior_cost_kernel(int S, int N, const int32_t *n_frames, const int32_t *active,
+                                         const double *frame_cost, double *cost) {
     const int s = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
-    if (s >= S) return;
+    if (s >= S || (active && !active[s])) return;
     const int nf = n_frames[s];
     double a0 = 0.0, a1 = 0.0;
     for (int k = lane; k < nf; k += 32) {
@@ -234,7 +235,7 @@ extern "C" int cpe_prior_cost_f64(const cpe_model *model, const cpe_prior *prior
     prior_kernel<false><<<dim3(b->N, b->S), 128, 0, (cudaStream_t)stream>>>(p);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return (int)e;
-    reduce_prior_cost_kernel<<<(b->S + 3) / 4, 128, 0, (cudaStream_t)stream>>>(b->S, b->N, b->n_frames, frame_work, prior_cost);
+    reduce_prior_cost_kernel<<<(b->S + 3) / 4, 128, 0, (cudaStream_t)stream>>>(b->S, b->N, b->n_frames, b->active, frame_work, prior_cost);
     return (int)cudaGetLastError();
 }
 
@@ -274,6 +275,7 @@ __global__ void __launch_bounds__(256) band_general_kernel(const __grid_constant
     const int N = p.b.N, bw = p.bw, WN = bw + 1;
     const int nf = p.b.n_frames[s];
     const int n = nf * NX;
+    if (p.b.active && !p.b.active[s]) return;
     double *Wn = smg;                    // [WN][WN]
     double *lcol = Wn + WN * WN;         // [WN]
     double *bvec = lcol + WN;            // [WN] running right-hand side

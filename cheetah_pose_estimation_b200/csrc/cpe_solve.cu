@@ -36,7 +36,7 @@ __global__ void __launch_bounds__(128) step_apply_kernel(const __grid_constant__
     const int N = p.b.N;
     if (fidx >= p.b.S * N) return;
     const int s = fidx / N, k = fidx - s * N;
-    if (k >= p.b.n_frames[s]) return;
+    if (k >= p.b.n_frames[s] || (p.b.active && !p.b.active[s])) return;
     double *d = dl[wid];
     const double *di = p.delta_ind + (size_t)fidx * 28;
     for (int c = lane; c < 54; c += 32) {
@@ -71,10 +71,11 @@ __global__ void __launch_bounds__(128) step_apply_kernel(const __grid_constant__
 }
 
 // ---- deterministic per-sequence reduction ------------------------------------------------------------------------
-__global__ void reduce_cost_kernel(int S, int N, const int32_t *n_frames, const double *frame_cost, double *cost) {
+__global__ void reduce_cost_kernel(int S, int N, const int32_t *n_frames, const int32_t *active, const double *frame_cost,
+                                   double *cost) {
     const int s = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
-    if (s >= S) return;
+    if (s >= S || (active && !active[s])) return;
     const int nf = n_frames[s];
     double a[4] = {0, 0, 0, 0};
     for (int k = lane; k < nf; k += 32) {
@@ -155,7 +156,7 @@ extern "C" int cpe_version(void) { return CPE_VERSION; }
 
 extern "C" int cpe_reduce_cost_f64(const cpe_batch *b, const double *frame_cost, double *cost, void *stream) {
     if (!b || !frame_cost || !cost) return CPE_E_NULL;
-    cpe::reduce_cost_kernel<<<(b->S + 3) / 4, 128, 0, (cudaStream_t)stream>>>(b->S, b->N, b->n_frames, frame_cost, cost);
+    cpe::reduce_cost_kernel<<<(b->S + 3) / 4, 128, 0, (cudaStream_t)stream>>>(b->S, b->N, b->n_frames, b->active, frame_cost, cost);
     return (int)cudaGetLastError();
 }
 

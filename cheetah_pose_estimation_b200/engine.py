@@ -71,6 +71,7 @@ class Batch:
     mu_in: float = 1e4
     loss: tuple = (3.0, 10.0, 20.0)
     dlc_thresh: float = 0.5
+    active: torch.Tensor = None  # [S] int32, optional: sequences with 0 are skipped by every kernel
 
     @property
     def meas_layout(self):
@@ -113,6 +114,7 @@ class Batch:
         b.meas, b.cams, b.chain_vec = self.meas.data_ptr(), self.cams.data_ptr(), self.chain_vec.data_ptr()
         b.lam_eq = self.lam_eq.data_ptr() if self.lam_eq is not None else None
         b.lam_in = self.lam_in.data_ptr() if self.lam_in is not None else None
+        b.active = self.active.data_ptr() if self.active is not None else None
         return b
 
     def window(self, s0, s1):
@@ -121,7 +123,8 @@ class Batch:
                      chain_vec=self.chain_vec[s0:s1], cam_model=self.cam_model,
                      lam_eq=None if self.lam_eq is None else self.lam_eq[s0:s1],
                      lam_in=None if self.lam_in is None else self.lam_in[s0:s1],
-                     mu_eq=self.mu_eq, mu_in=self.mu_in, loss=self.loss, dlc_thresh=self.dlc_thresh)
+                     mu_eq=self.mu_eq, mu_in=self.mu_in, loss=self.loss, dlc_thresh=self.dlc_thresh,
+                     active=None if self.active is None else self.active[s0:s1])
 
     @staticmethod
     def from_numpy(meas, cams, chain_vec, h, n_frames=None, device="cuda", cam_model=FISHEYE, meas_dtype=torch.float32,
@@ -329,7 +332,8 @@ class Solver:
         return self.delta, self.q_try, self.frame_pred
 
     # ---- full LM / AL loop -----------------------------------------------------------------------------------------
-    def solve(self, q0, max_iter=40, n_outer=4, damp0=1e-3, ftol=1e-6, mu_schedule=(1e4, 1e5, 1e6, 1e6), check_every=1):
+    def solve(self, q0, max_iter=40, n_outer=4, damp0=1e-3, ftol=1e-6, mu_schedule=(1e4, 1e5, 1e6, 1e6), check_every=1,
+              skip_converged=True):
         """Minimise the reference objective over q starting from q0[S,N,54]; returns a dict of device tensors.
 
         Outer loop = augmented-Lagrangian multiplier updates with penalty continuation; inner loop = LM with
@@ -355,8 +359,10 @@ class Solver:
                 self.state[0].add_(self.prior_cost.sum(dim=1))
             self.active.fill_(1)
             for it in range(max_iter):
+                b.active = self.active if skip_converged else None      # converged sequences cost nothing from here on
                 self.lm_step(q, damp)
                 self.evaluate(self.q_try, cost_out=cost_try, prior_out=prior_try)
+                b.active = None
                 bs = b.struct()
                 if self.priors is not None:
                     _lib.check(lib.cpe_step_accept_prior_f64(C.byref(bs), _ptr(cost_try), _ptr(prior_try),

@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 105          /* 0.1.5 */
+#define CPE_VERSION 106          /* 0.1.6 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -119,6 +119,8 @@ typedef struct cpe_batch {
     const double *chain_vec;        /* [S,24,5,3] body-frame vectors of the marker chains */
     const double *lam_eq;           /* [S,N,26] multipliers (may be NULL = 0) */
     const double *lam_in;           /* [S,N,n_ineq] (may be NULL = 0) */
+    const int32_t *active;          /* [S] optional (NULL = all): sequences with active == 0 are skipped by every kernel
+                                       (their outputs keep their previous contents) -- converged sequences of an LM loop */
 } cpe_batch;
 
 /* Optional outputs of cpe_eval (NULL = skip). */

