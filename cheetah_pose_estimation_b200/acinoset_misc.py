@@ -123,18 +123,39 @@ def load_dlc_arrays(dlc_dir, n_cams=None):
     return [_read_dlc_file(p) for p in files]
 
 
-def pack_measurements(params: TrajectoryParams, scene: Scene, base_data):
-    """meas[N,C,24,1,4] float32 = (u, v, gate, 0) in marker order, C = all cameras or the single monocular one.
+PW_SUFFIX = "DLC_resnet152_CheetahOct14shuffle4_650000.pickle"      # acinoset_misc.py:203-205
+
+
+def load_pairwise(dlc_dir, n_cams=None):
+    """Pairwise pseudo-measurement files of `enable_ppm` (acinoset_misc.py:200-205): `<dlc_dir>_pw/<first 4 characters
+    of the camera's DLC file name>DLC_resnet152_..._650000.pickle`, one per camera; each is indexable by frame row and
+    yields {"pose": [75] (x, y, likelihood per DLC part), "pws": [k, 25, 25, 2] pairwise offsets}."""
+    import pickle
+    out = []
+    for path in dlc_files(dlc_dir):
+        with open(os.path.join(dlc_dir + "_pw", os.path.basename(path)[:4] + PW_SUFFIX), "rb") as f:
+            out.append(pickle.load(f))
+    if n_cams is not None:
+        assert n_cams == len(out)
+    return out
+
+
+def pack_measurements(params: TrajectoryParams, scene: Scene, base_data, pw_data=None):
+    """meas[N,C,24,W,4] float32 = (u, v, gate, 0) in marker order, C = all cameras or the single monocular one.
     Row of camera c for frame n: (n-1) + start_frame - sync_offset[c]  (acinoset_misc.py:224, 246); gate =
-    likelihood > dlc_thresh (strict, :231).  NaN detections get gate 0 (documented divergence)."""
+    likelihood > dlc_thresh (strict, :231).  NaN detections get gate 0 (documented divergence).
+    W = 1, or 3 with `params.enable_ppms`: hypotheses w = 2, 3 are pairwise pseudo-measurements
+    `pose[base] + pws[0, base, dlc_index[marker]]` with `base = pairwise_graph[marker][w-2]`, gated by the
+    likelihood of the base part (acinoset_misc.py:225-228, 249-254)."""
     N = params.end_frame - params.start_frame
+    W = 3 if params.enable_ppms else 1
     sync = [0] * scene.n_cams
     if params.sync_offset is not None:
         for off in params.sync_offset:
             sync[off["cam"]] = off["frame"]
     cams = list(range(scene.n_cams)) if scene.cam_idx is None else [scene.cam_idx]
     idx = np.array(sk.DLC_INDEX)
-    meas = np.zeros((N, len(cams), 24, 1, 4), np.float32)
+    meas = np.zeros((N, len(cams), 24, W, 4), np.float32)
     for ci, c in enumerate(cams):
         rows = np.arange(N) + params.start_frame - sync[c]
         d = np.asarray(base_data[c])[rows]
@@ -146,6 +167,22 @@ def pack_measurements(params: TrajectoryParams, scene: Scene, base_data):
         meas[:, ci, :, 0, 0] = np.where(bad, 0.0, x)
         meas[:, ci, :, 0, 1] = np.where(bad, 0.0, y)
         meas[:, ci, :, 0, 2] = gate
+        if W == 3:
+            assert pw_data is not None, "enable_ppm needs the dlc_pw/*.pickle files (load_pairwise)"
+            pair = np.array(sk.PAIRWISE)                                   # [24, 2] DLC part indices
+            for n in range(N):
+                values = pw_data[c][int(rows[n])]
+                pose = np.asarray(values["pose"], dtype=np.float64)
+                pws = np.asarray(values["pws"], dtype=np.float64)
+                for w in (1, 2):
+                    base = pair[:, w - 1]
+                    xw = pose[0::3][base] + pws[0, base, idx, 0]
+                    yw = pose[1::3][base] + pws[0, base, idx, 1]
+                    lw = pose[2::3][base]
+                    badw = ~(np.isfinite(xw) & np.isfinite(yw) & np.isfinite(lw))
+                    meas[n, ci, :, w, 0] = np.where(badw, 0.0, xw)
+                    meas[n, ci, :, w, 1] = np.where(badw, 0.0, yw)
+                    meas[n, ci, :, w, 2] = (lw > params.dlc_thresh) & ~badw
     return meas, cams
 
 

@@ -137,9 +137,6 @@ def init_trajectory(root_dir: str,
         raise NotImplementedError("kinetic (physics-based) model: out of scope of this path (SURVEY.md section 8f.3)")
     if shutter_delay_estimation:
         raise NotImplementedError("shutter-delay estimation is not on this path (SURVEY.md section 8f.4)")
-    if enable_ppm:
-        raise NotImplementedError("pairwise pseudo-measurement files (dlc_pw/*.pickle) are not read yet; the kernels "
-                                  "accept W = 3 (SURVEY.md section 8f.4)")
     if cheetah_name not in ("jules", "phantom", "shiraz", "arabia"):
         cheetah_name = "acinoset"
     ground_plane_height = 0.0
@@ -179,7 +176,8 @@ def init_trajectory(root_dir: str,
     if include_camera_constraints:
         print("Create camera constraints based on DLC predictions")
         est.base_data = misc.load_dlc_arrays(dlc_dir, scene.n_cams)
-        est.meas, est.cams_used = misc.pack_measurements(params, scene, est.base_data)
+        pw_data = misc.load_pairwise(dlc_dir, scene.n_cams) if enable_ppm else None
+        est.meas, est.cams_used = misc.pack_measurements(params, scene, est.base_data, pw_data)
     _ = (ground_plane_height, disable_contact_lcp, bound_eom_error, solver_path)     # kinetic-mode / IPOPT settings
     return est
 

@@ -89,3 +89,57 @@ def test_trajectory_estimate_tracks_the_spine(golden_dir, tmp_path):
     heading = g["q"][:, 5]
     dpsi = np.angle(np.exp(1j * (psi[fr] - heading)))
     assert np.abs(dpsi).max() < 0.5
+
+
+def test_pairwise_pseudo_measurements_follow_the_reference_indexing(tmp_path):
+    """enable_ppm (W = 3): literal per-element restatement of acinoset_misc.py:211-256 against pack_measurements."""
+    import pickle
+    from cheetah_pose_estimation_b200 import acinoset_misc as misc, skeleton as sk
+    rng = np.random.default_rng(5)
+    n_cams, n_rows, start, N = 2, 14, 3, 6
+    dlc_dir = tmp_path / "dlc"
+    (tmp_path / "dlc_pw").mkdir()
+    dlc_dir.mkdir()
+    base_data, pw_files = [], []
+    for c in range(n_cams):
+        arr = rng.uniform(0, 1000, (n_rows, 75))
+        arr[:, 2::3] = rng.uniform(0, 1, (n_rows, 25))
+        np.save(dlc_dir / f"cam{c + 1}DLC_x.npy", arr)
+        base_data.append(arr)
+        pw = [{"pose": np.concatenate([rng.uniform(0, 1000, 50), rng.uniform(0, 1, 25)])[np.argsort(np.tile(np.arange(25), 3), kind="stable")],
+               "pws": rng.normal(0, 20, (2, 25, 25, 2))} for _ in range(n_rows)]
+        for v in pw:                                                        # (x, y, lik) interleaved per part
+            p = np.empty(75)
+            p[0::3], p[1::3], p[2::3] = rng.uniform(0, 1000, 25), rng.uniform(0, 1000, 25), rng.uniform(0, 1, 25)
+            v["pose"] = p
+        with open(tmp_path / "dlc_pw" / f"cam{c + 1}{misc.PW_SUFFIX}", "wb") as f:
+            pickle.dump(pw, f)
+        pw_files.append(pw)
+    sync = [{"cam": 1, "frame": 2}]
+    params = misc.TrajectoryParams(str(tmp_path), start, start + N, N, 0.5, sync, False, False, False, True)
+    scene = misc.Scene("", None, None, None, None, None, 90, n_cams, None)
+    pw_data = misc.load_pairwise(str(dlc_dir), n_cams)
+    meas, cams = misc.pack_measurements(params, scene, misc.load_dlc_arrays(str(dlc_dir), n_cams), pw_data)
+    assert meas.shape == (N, n_cams, 24, 3, 4) and cams == [0, 1]
+    # the reference's dictionaries (acinoset_misc.py:1943-1998), from the pinned tables
+    index_dict = dict(zip(sk.MARKERS, sk.DLC_INDEX))
+    pair_dict = dict(zip(sk.MARKERS, sk.PAIRWISE))
+    sync_arr = [0, 2]
+    for n in range(1, N + 1):
+        for c in range(1, n_cams + 1):
+            row = (n - 1) + start - sync_arr[c - 1]
+            for l, marker in enumerate(sk.MARKERS):
+                for w in (1, 2, 3):
+                    if w < 2:
+                        base = index_dict[marker]
+                        lik = base_data[c - 1][row][2::3][base]
+                        val = [base_data[c - 1][row][d::3][base] for d in (0, 1)]
+                    else:
+                        values = pw_files[c - 1][row]
+                        base = pair_dict[marker][w - 2]
+                        lik = values["pose"][2::3][base]
+                        val = [values["pose"][d::3][base] + values["pws"][:, :, :, d][0, base, index_dict[marker]]
+                               for d in (0, 1)]
+                    got = meas[n - 1, c - 1, l, w - 1]
+                    assert got[0] == np.float32(val[0]) and got[1] == np.float32(val[1])
+                    assert got[2] == (1.0 if lik > 0.5 else 0.0)
