@@ -48,6 +48,7 @@ def parse_args():
     ap.add_argument("--wave", type=int, default=512, help="sequences per launch (Jacobian buffer reuse)")
     ap.add_argument("--lm-seqs", type=int, default=444, help="sequences of the LM-solve leg (0 = skip)")
     ap.add_argument("--lm-iters", type=int, default=20)
+    ap.add_argument("--lm-split", type=int, default=1, help="sub-batches of the LM leg solved on separate streams")
     ap.add_argument("--cpu-seqs", type=int, default=64, help="sequences of the cpu_baseline sample (0 = skip)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-f32", action="store_true", help="skip the FP32-flavour leg")
@@ -326,14 +327,12 @@ def lm_leg(a, r):
     if S_lm <= 0:
         return None
     bw = r["batch"].window(0, S_lm)
-    solver = engine.Solver(r["model"], bw)
     q0 = r["q_init"][:S_lm].contiguous()
-    solver.solve(q0, max_iter=2, n_outer=1)            # warm-up (lazy module load, allocator)
+    engine.solve_split(r["model"], bw, q0, n_split=a.lm_split, max_iter=2, n_outer=1)   # warm-up (module load, allocator)
     r["barrier"]()
-    l0 = solver.launches
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    res = solver.solve(q0, max_iter=a.lm_iters, n_outer=3)
+    res = engine.solve_split(r["model"], bw, q0, n_split=a.lm_split, max_iter=a.lm_iters, n_outer=3)
     e1.record()
     r["barrier"]()
     ms = e0.elapsed_time(e1)
@@ -342,7 +341,7 @@ def lm_leg(a, r):
     f0 = None
     return {"sequences": S_lm, "sequences_per_s": S_lm / (ms * 1e-3), "ms": ms,
             "lockstep_iterations": res["lockstep_iterations"], "mean_iterations": cnt[0], "mean_accepted": cnt[1],
-            "launches": solver.launches - l0, "final_cost_mean": float(res["cost"][:, :2].sum(dim=1).mean()),
+            "launches": res["launches"], "streams": a.lm_split, "final_cost_mean": float(res["cost"][:, :2].sum(dim=1).mean()),
             "max_abs_joint_violation": ceq, "failed_pivots": int(res["status"].sum()),
             "ms_per_lockstep_iteration": ms / max(1, res["lockstep_iterations"]),
             "settings": {"n_outer": 3, "max_iter": a.lm_iters, "ftol": 1e-6}}

@@ -22,7 +22,7 @@ class CpeModel(C.Structure):
         ("u_off", c_i32p), ("u_item", c_i32p), ("col_item", c_i32p),
         ("ent_pq", c_i32p), ("a_ptr", c_i32p), ("a_items", c_i32p), ("e_ptr", c_i32p), ("e_items", c_i32p),
         ("i_ptr", c_i32p), ("i_items", c_i32p), ("diag_ent", c_i32p), ("grad_ent", c_i32p), ("grp_src", c_i32p),
-        ("s_src", c_i32p), ("s_ptr", c_i32p), ("s_items", c_i32p),
+        ("s_src", c_i32p), ("s_ptr", c_i32p), ("s_items", c_i32p), ("ent_order", c_i32p), ("s_order", c_i32p),
     ]
 
 

@@ -237,7 +237,8 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
     }
     __syncthreads();
     // ---- every Hessian / gradient nonzero = one gather over its static item list -------------------------------------
-    for (int e = tid; e < n_ent; e += nt) {
+    for (int eo = tid; eo < n_ent; eo += nt) {
+        const int e = p.m.ent_order[eo];                 // lanes of a warp get gather lists of similar length
         const int pq = p.m.ent_pq[e];
         const int pp = pq >> 6, qq = pq & 63;
         const bool grad = qq == GRAD_Q;
@@ -326,7 +327,8 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
     __syncthreads();
     // ---- reduced block S = H_ii + damping - sum_g Hdi^T Y and ghat = g_i - sum_g Hdi^T y (static gather) ----------------
     double *So = p.ao.S + fidx * 784;
-    for (int e = tid; e < 28 * 29; e += nt) {
+    for (int eo = tid; eo < 28 * 29; eo += nt) {
+        const int e = p.m.s_order[eo];
         const int r = e / 29, c = e - r * 29;
         double v;
         if (c == 28) {
@@ -371,7 +373,7 @@ extern "C" int cpe_assemble_f64(const cpe_model *model, const cpe_batch *b, cons
     if (model->n_u != 198 || model->n_ent <= 0 || model->n_ent > ENT_PAD) return CPE_E_DIM;
     if (!model->ent_pq || !model->a_ptr || !model->a_items || !model->e_ptr || !model->e_items || !model->i_ptr ||
         !model->i_items || !model->diag_ent || !model->grad_ent || !model->grp_src || !model->s_src || !model->s_ptr ||
-        !model->s_items)
+        !model->s_items || !model->ent_order || !model->s_order)
         return CPE_E_NULL;
     if (out->S && (!damp || !out->ghat || !out->Y || !out->y)) return CPE_E_NULL;
     AsmParams p;

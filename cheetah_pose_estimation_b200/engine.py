@@ -16,7 +16,7 @@ FISHEYE, PINHOLE = 0, 1
 MEAS_F32X4, MEAS_F64X4, MEAS_F32X3 = 0, 1, 2      # include/cpe.h CPE_MEAS_*
 _I32_KEYS = ("chain_link", "eq_pairs", "ineq_idx", "ind_idx", "ind_pos", "grp_ndep", "grp_nnb", "grp_dep", "grp_nb",
              "u_off", "u_item", "col_item", "ent_pq", "a_ptr", "a_items", "e_ptr", "e_items", "i_ptr", "i_items", "diag_ent",
-             "grad_ent", "grp_src", "s_src", "s_ptr", "s_items")
+             "grad_ent", "grp_src", "s_src", "s_ptr", "s_items", "ent_order", "s_order")
 _F64_KEYS = ("ineq_bounds", "wq", "meas_w")
 
 
@@ -298,6 +298,19 @@ class Solver:
 
     # ---- K3 --------------------------------------------------------------------------------------------------
     def band_solve(self):
+        hp = getattr(self, "k3_stream", None)
+        if hp is None:
+            return self._band_solve()
+        # K3 on a high-priority stream: its few, long-lived CTAs get SM slots ahead of the queued K2 CTAs of another
+        # sub-batch (solve_split), which is what lets the latency-bound sweep overlap the throughput-bound assembly
+        cur = torch.cuda.current_stream()
+        hp.wait_stream(cur)
+        with torch.cuda.stream(hp):
+            out = self._band_solve()
+        cur.wait_stream(hp)
+        return out
+
+    def _band_solve(self):
         if self.priors is not None:
             bs = self.b.struct()
             _lib.check(self.lib.cpe_band_solve_general_f64(
@@ -332,12 +345,21 @@ class Solver:
         return self.delta, self.q_try, self.frame_pred
 
     # ---- full LM / AL loop -----------------------------------------------------------------------------------------
-    def solve(self, q0, max_iter=40, n_outer=4, damp0=1e-3, ftol=1e-6, mu_schedule=(1e4, 1e5, 1e6, 1e6), check_every=1,
-              skip_converged=True):
+    def solve(self, q0, **kw):
         """Minimise the reference objective over q starting from q0[S,N,54]; returns a dict of device tensors.
 
         Outer loop = augmented-Lagrangian multiplier updates with penalty continuation; inner loop = LM with
-        per-sequence damping (all sequences advance in lock step; converged ones are masked)."""
+        per-sequence damping (all sequences advance in lock step; converged ones are masked and skipped).
+        Keywords: max_iter=40, n_outer=4, damp0=1e-3, ftol=1e-6, mu_schedule, check_every=1, skip_converged=True."""
+        for _ in self.solve_steps(q0, **kw):
+            pass
+        return self.result
+
+    def solve_steps(self, q0, max_iter=40, n_outer=4, damp0=1e-3, ftol=1e-6, mu_schedule=(1e4, 1e5, 1e6, 1e6),
+                    check_every=1, skip_converged=True):
+        """Generator form of `solve`: yields after the launches of every LM iteration have been queued (before the
+        host looks at the convergence flags), so that a driver can interleave several solvers on different streams
+        (`solve_split`).  The result dict is left in `self.result`."""
         b, lib = self.b, self.lib
         S, N, dev = b.S, b.N, q0.device
         q = q0.clone().contiguous()
@@ -376,6 +398,7 @@ class Solver:
                                "cpe_step_accept_f64")
                 self.launches += 1
                 total_inner += 1
+                yield total_inner
                 if (it + 1) % check_every == 0 and not bool(self.active.any()):
                     break
             self.evaluate(q, constraints=True)
@@ -389,7 +412,44 @@ class Solver:
                    status=self.status.clone(), lockstep_iterations=total_inner)
         if self.priors is not None:
             res["prior_cost"] = out["prior_cost"].clone()
-        return res
+        self.result = res
+
+
+def solve_split(model, batch, q0, n_split=2, priors=None, **kw):
+    """LM-solve `batch` as `n_split` independent sub-batches on their own CUDA streams, launches interleaved from one
+    host thread.  The block-banded solve K3 is a latency-bound sweep along time (one CTA per sequence, ~10 % issue
+    utilisation) while the assembly K2 is throughput-bound, so K3 of one sub-batch overlaps K2 of the other.  Per-sequence
+    results are bit-identical to `Solver.solve` (no cross-sequence arithmetic anywhere).  Returns the same dict."""
+    S = batch.S
+    n_split = max(1, min(n_split, S))
+    cuts = [S * i // n_split for i in range(n_split + 1)]
+    cur = torch.cuda.current_stream()
+    streams = [torch.cuda.Stream(device=model.device) for _ in range(n_split)]
+    solvers, gens = [], []
+    for i, st in enumerate(streams):
+        st.wait_stream(cur)
+        with torch.cuda.stream(st):
+            sv = Solver(model, batch.window(cuts[i], cuts[i + 1]), priors=priors)
+            if n_split > 1:
+                sv.k3_stream = torch.cuda.Stream(device=model.device, priority=-1)
+            solvers.append(sv)
+            gens.append(sv.solve_steps(q0[cuts[i]:cuts[i + 1]].contiguous(), **kw))
+    live = list(range(n_split))
+    while live:
+        for i in list(live):
+            with torch.cuda.stream(streams[i]):
+                try:
+                    next(gens[i])
+                except StopIteration:
+                    live.remove(i)
+    for st in streams:
+        cur.wait_stream(st)
+    res = {}
+    for k in solvers[0].result:
+        vals = [sv.result[k] for sv in solvers]
+        res[k] = max(vals) if k == "lockstep_iterations" else torch.cat(vals, dim=0)
+    res["launches"] = sum(sv.launches for sv in solvers)
+    return res
 
 
 class HostEvaluator:

@@ -461,6 +461,13 @@ def assemble_tables(t=None, kinetic_dataset=False):
                 elif nbpos[g, c] >= 0:
                     s_items.append((g << 8) | (a << 4) | int(nbpos[g, c]))
             s_ptr.append(len(s_items))
+    # processing orders, heaviest gather lists first: the 32 lanes of a warp then work on lists of similar length
+    # (the order of the items inside a list -- hence every sum -- is unchanged)
+    s_ptr = np.array(s_ptr, np.int32)
+    work = 3 * np.diff(a_ptr) + np.diff(e_ptr) + np.diff(i_ptr)
+    ent_order = np.argsort(-work, kind="stable").astype(np.int32)
+    s_order = np.argsort(-np.diff(s_ptr), kind="stable").astype(np.int32)
     return dict(n_ent=len(keys), ent_pq=ent_pq, a_ptr=a_ptr, a_items=a_items, e_ptr=e_ptr, e_items=e_items,
                 i_ptr=i_ptr, i_items=i_items, diag_ent=diag_ent, grad_ent=grad_ent, grp_src=grp_src.reshape(-1),
-                s_src=s_src.reshape(-1), s_ptr=np.array(s_ptr, np.int32), s_items=np.array(s_items, np.int32))
+                s_src=s_src.reshape(-1), s_ptr=s_ptr, s_items=np.array(s_items, np.int32), ent_order=ent_order,
+                s_order=s_order)

@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 106          /* 0.1.6 */
+#define CPE_VERSION 107          /* 0.1.7 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -102,6 +102,8 @@ typedef struct cpe_model {
     const int32_t *s_src;           /* [28*28] entry of H(ind_r, ind_c) or -1 */
     const int32_t *s_ptr;           /* [28*29+1] Schur items of S(r,c) (c = 28: ghat): (group << 8) | (a << 4) | b */
     const int32_t *s_items;
+    const int32_t *ent_order;       /* [n_ent] processing order of the entries, longest gather list first */
+    const int32_t *s_order;         /* [28*29] processing order of the Schur items, longest list first */
 } cpe_model;
 
 /* One batch of sequences. */

@@ -337,3 +337,16 @@ def test_skipping_converged_sequences_changes_nothing(gpu):
     for k in ("q", "cost", "counters"):
         assert torch.equal(res[0][k], res[1][k]), k
     assert int(res[0]["counters"][:, 0].min()) < int(res[0]["counters"][:, 0].max()) or True
+
+
+def test_solve_split_is_bit_identical(gpu):
+    """Two sub-batches on two streams (K3 of one overlapping K2 of the other) == one batch."""
+    import torch
+    from cheetah_pose_estimation_b200 import engine, synthetic
+    prob = synthetic.make_problem(S=5, N=16, C=6, seed=43)
+    q0 = torch.as_tensor(prob.q_init, device="cuda:0")
+    one = engine.Solver(gpu, prob.to_batch("cuda:0")).solve(q0, max_iter=10, n_outer=2)
+    two = engine.solve_split(gpu, prob.to_batch("cuda:0"), q0, n_split=2, max_iter=10, n_outer=2)
+    torch.cuda.synchronize()
+    for k in ("q", "cost", "counters", "c_eq"):
+        assert torch.equal(one[k], two[k]), k
