@@ -29,7 +29,8 @@ class CpeModel(C.Structure):
 class CpeBatch(C.Structure):
     _fields_ = [
         ("S", C.c_int32), ("N", C.c_int32), ("C", C.c_int32), ("W", C.c_int32),
-        ("cam_model", C.c_int32), ("meas_layout", C.c_int32), ("dlc_thresh", C.c_double),
+        ("cam_model", C.c_int32), ("meas_layout", C.c_int32), ("loss_mode", C.c_int32), ("reserved0", C.c_int32),
+        ("dlc_thresh", C.c_double),
         ("mu_eq", C.c_double), ("mu_in", C.c_double),
         ("loss_a", C.c_double), ("loss_b", C.c_double), ("loss_c", C.c_double),
         ("n_frames", c_i32p), ("h", c_f64p), ("meas", C.c_void_p), ("cams", c_f64p), ("chain_vec", c_f64p),

@@ -157,11 +157,17 @@ def pack_measurements(params: TrajectoryParams, scene: Scene, base_data, pw_data
     idx = np.array(sk.DLC_INDEX)
     meas = np.zeros((N, len(cams), 24, W, 4), np.float32)
     for ci, c in enumerate(cams):
-        rows = np.arange(N) + params.start_frame - sync[c]
-        d = np.asarray(base_data[c])[rows]
-        x, y, lik = d[:, 0::3][:, idx], d[:, 1::3][:, idx], d[:, 2::3][:, idx]
         if params.hand_labeled_data:
+            # hand labels: (x, y) pairs per part, rows NOT shifted by the sync offset, likelihood 1
+            # (acinoset_misc.py:216-221, 241-242)
+            rows = np.arange(N) + params.start_frame
+            d = np.asarray(base_data[c])[rows]
+            x, y = d[:, 0::2][:, idx], d[:, 1::2][:, idx]
             lik = np.ones_like(x)
+        else:
+            rows = np.arange(N) + params.start_frame - sync[c]
+            d = np.asarray(base_data[c])[rows]
+            x, y, lik = d[:, 0::3][:, idx], d[:, 1::3][:, idx], d[:, 2::3][:, idx]
         bad = ~(np.isfinite(x) & np.isfinite(y) & np.isfinite(lik))
         gate = (lik > params.dlc_thresh) & ~bad
         meas[:, ci, :, 0, 0] = np.where(bad, 0.0, x)

@@ -187,12 +187,17 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
             double um, vm, gate;
             if (w > 0) meas_fetch(p.b, midx0 + w, mraw);
             meas_unpack(p.b, mraw, um, vm, gate);
-            const double wgt = gate * p.m.meas_w[w * 24 + ml] * cmult;
+            const bool sq = p.b.loss_mode == CPE_LOSS_SQUARE;
+            const double wgt = gate * p.m.meas_w[w * 24 + ml] * (sq ? 1.0 : cmult);
             const double eu = wgt * (pr.u - um), ev = wgt * (pr.v - vm);
             const double Eu = fabs(eu), Ev = fabs(ev);
             double rho, du_, dv_;
-            redescending(Eu, la_, lb_, lc_, p.ea, p.eb, p.ec, rho, du_);
-            redescending(Ev, la_, lb_, lc_, p.ea, p.eb, p.ec, rho, dv_);
+            if (sq) {
+                du_ = 2.0 * Eu; dv_ = 2.0 * Ev;
+            } else {
+                redescending(Eu, la_, lb_, lc_, p.ea, p.eb, p.ec, rho, du_);
+                redescending(Ev, la_, lb_, lc_, p.ea, p.eb, p.ec, rho, dv_);
+            }
             gu += du_ * (eu > 0.0 ? 1.0 : (eu < 0.0 ? -1.0 : 0.0)) * wgt;
             gv += dv_ * (ev > 0.0 ? 1.0 : (ev < 0.0 ? -1.0 : 0.0)) * wgt;
             hu += (Eu > 0.0 ? fmax(du_ / Eu, 0.0) : 0.0) * wgt * wgt;

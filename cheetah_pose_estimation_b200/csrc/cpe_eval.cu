@@ -254,12 +254,17 @@ __global__ void __launch_bounds__(WPC * 32, MINB) eval_kernel(const __grid_const
                     if (w > 0) meas_fetch(p.b, mi + w, cur);
                     double um, vm, gate;
                     meas_unpack(p.b, cur, um, vm, gate);
-                    const T wgt = (T)(gate * p.m.meas_w[w * 24 + ml] * cmult);
+                    const bool sq = p.b.loss_mode == CPE_LOSS_SQUARE;
+                    const T wgt = (T)(gate * p.m.meas_w[w * 24 + ml] * (sq ? 1.0 : cmult));
                     // residual = (fx a s) + (cx - u_meas): the ~1000 px offsets cancel in FP64 before rounding to T
                     const T ru = pr.pu + (T)(cx - um), rv = pr.pv + (T)(cy - vm);
                     if (p.eo.resid) reinterpret_cast<T2 *>(p.eo.resid)[mi + w] = mk2(ru, rv);
-                    rho += redescending_value<T>(fabs(wgt * ru), la_, lb_, lc_, ea, eb, ec);
-                    rho += redescending_value<T>(fabs(wgt * rv), la_, lb_, lc_, ea, eb, ec);
+                    if (sq) {
+                        rho += (wgt * ru) * (wgt * ru) + (wgt * rv) * (wgt * rv);
+                    } else {
+                        rho += redescending_value<T>(fabs(wgt * ru), la_, lb_, lc_, ea, eb, ec);
+                        rho += redescending_value<T>(fabs(wgt * rv), la_, lb_, lc_, ea, eb, ec);
+                    }
                 }
                 if (JAC) {
                     T2 *d2 = reinterpret_cast<T2 *>(dp + 6 * lane);

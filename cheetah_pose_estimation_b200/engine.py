@@ -14,6 +14,7 @@ from . import _lib, skeleton
 
 FISHEYE, PINHOLE = 0, 1
 MEAS_F32X4, MEAS_F64X4, MEAS_F32X3 = 0, 1, 2      # include/cpe.h CPE_MEAS_*
+LOSS_REDESCENDING, LOSS_SQUARE = 0, 1             # include/cpe.h CPE_LOSS_*
 _I32_KEYS = ("chain_link", "eq_pairs", "ineq_idx", "ind_idx", "ind_pos", "grp_ndep", "grp_nnb", "grp_dep", "grp_nb",
              "u_off", "u_item", "col_item", "ent_pq", "a_ptr", "a_items", "e_ptr", "e_items", "i_ptr", "i_items", "diag_ent",
              "grad_ent", "grp_src", "s_src", "s_ptr", "s_items", "ent_order", "s_order")
@@ -71,6 +72,7 @@ class Batch:
     mu_in: float = 1e4
     loss: tuple = (3.0, 10.0, 20.0)
     dlc_thresh: float = 0.5
+    loss_mode: int = LOSS_REDESCENDING
     active: torch.Tensor = None  # [S] int32, optional: sequences with 0 are skipped by every kernel
 
     @property
@@ -107,6 +109,7 @@ class Batch:
         b.S, b.N, b.C, b.W = self.S, self.N, self.C, self.W
         b.cam_model = int(self.cam_model)
         b.meas_layout = self.meas_layout
+        b.loss_mode = int(self.loss_mode)
         b.dlc_thresh = float(self.dlc_thresh)
         b.mu_eq, b.mu_in = float(self.mu_eq), float(self.mu_in)
         b.loss_a, b.loss_b, b.loss_c = self.loss
@@ -124,11 +127,12 @@ class Batch:
                      lam_eq=None if self.lam_eq is None else self.lam_eq[s0:s1],
                      lam_in=None if self.lam_in is None else self.lam_in[s0:s1],
                      mu_eq=self.mu_eq, mu_in=self.mu_in, loss=self.loss, dlc_thresh=self.dlc_thresh,
+                     loss_mode=self.loss_mode,
                      active=None if self.active is None else self.active[s0:s1])
 
     @staticmethod
     def from_numpy(meas, cams, chain_vec, h, n_frames=None, device="cuda", cam_model=FISHEYE, meas_dtype=torch.float32,
-                   dlc_native=False, dlc_thresh=0.5):
+                   dlc_native=False, dlc_thresh=0.5, loss_mode=LOSS_REDESCENDING):
         """meas[S,N,C,24,W,3|4] (u, v, gate), cams[S,C,24], chain_vec[S,24,5,3], h[S].  With dlc_native=True the
         last axis is the DLC triple (x, y, likelihood) and is kept as float3 records (gated on the device)."""
         meas = np.asarray(meas)
@@ -147,7 +151,7 @@ class Batch:
             meas=torch.as_tensor(np.ascontiguousarray(meas), device=dev).to(meas_dtype).contiguous(),
             cams=torch.as_tensor(np.ascontiguousarray(cams, dtype=np.float64), device=dev),
             chain_vec=torch.as_tensor(np.ascontiguousarray(chain_vec, dtype=np.float64), device=dev),
-            cam_model=cam_model, dlc_thresh=dlc_thresh)
+            cam_model=cam_model, dlc_thresh=dlc_thresh, loss_mode=loss_mode)
 
 
 class Solver:

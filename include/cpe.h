@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 107          /* 0.1.7 */
+#define CPE_VERSION 108          /* 0.1.8 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -60,6 +60,9 @@ extern "C" {
 #define CPE_MEAS_F64X4 1         /* double4 {u, v, gate, unused} */
 #define CPE_MEAS_F32X3 2         /* float3  {x, y, likelihood}: the DLC-native triple (acinoset_misc.py:237-256); the
                                     strict test likelihood > dlc_thresh (acinoset_misc.py:231) runs on the device */
+
+#define CPE_LOSS_REDESCENDING 0  /* acinoset_misc.py:476-482, 2001-2015 */
+#define CPE_LOSS_SQUARE 1        /* hand-labelled data: (w slack)^2, camera multiplier not applied (acinoset_misc.py:471-474) */
 
 #define CPE_E_ARG (-1)
 #define CPE_E_DIM (-2)
@@ -111,6 +114,8 @@ typedef struct cpe_batch {
     int32_t S, N, C, W;
     int32_t cam_model;              /* CPE_CAM_FISHEYE / CPE_CAM_PINHOLE */
     int32_t meas_layout;            /* CPE_MEAS_* */
+    int32_t loss_mode;              /* CPE_LOSS_* */
+    int32_t reserved0;
     double dlc_thresh;              /* likelihood threshold of CPE_MEAS_F32X3 (reference default 0.5) */
     double mu_eq, mu_in;            /* augmented-Lagrangian penalties */
     double loss_a, loss_b, loss_c;  /* redescending loss break points (3, 10, 20) */

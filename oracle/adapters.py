@@ -12,14 +12,16 @@ def oracle_weights(gate, cams, W=1, kinetic_dataset=False):
 
 
 def problem_from_arrays(meas, cams, chain_link, chain_vec, h, cam_model=cameras.FISHEYE, kinetic_dataset=False,
-                        mu=1e4):
+                        mu=1e4, square_loss=False):
     """meas[N,C,24,W,4] (u,v,gate,_), cams[C,24] -> cost.Problem for ONE sequence."""
     meas = np.asarray(meas, float)
     wgt = oracle_weights(meas[..., 2], cams, meas.shape[3], kinetic_dataset)
+    if square_loss:                                   # the camera multiplier is not applied in this branch (:471-474)
+        wgt = wgt / np.asarray(cams, float)[None, :, None, None, 20]
     m3 = np.concatenate([meas[..., 0:2], wgt[..., None]], -1)
     return cost.Problem(meas=m3, cams=np.asarray(cams, float)[:, :20], chain_link=chain_link, chain_vec=chain_vec,
                         h=float(h), cam_model=cam_model, ineq_rows=kinematics.inequality_rows(kinetic_dataset),
-                        mu_eq=mu, mu_in=mu)
+                        mu_eq=mu, mu_in=mu, square_loss=square_loss)
 
 
 def from_synthetic(prob, s, mu=1e4):

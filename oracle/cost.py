@@ -77,6 +77,7 @@ class Problem:
     ineq_rows: list = field(default_factory=kinematics.inequality_rows)
     mu_eq: float = 1e4
     mu_in: float = 1e4
+    square_loss: bool = False             # hand-labelled data: plain (w slack)^2 (acinoset_misc.py:471-474)
 
     @property
     def n_frames(self):
@@ -93,6 +94,8 @@ def residuals(pb: Problem, q):
 def measurement_cost(pb: Problem, q):
     r = residuals(pb, q)
     e = pb.meas[..., 2:3] * r
+    if pb.square_loss:
+        return float(np.sum(e * e))
     return float(np.sum(redescending_loss(e)))
 
 
@@ -159,8 +162,12 @@ def frame_normal_equations(pb: Problem, q, lam_eq=None, lam_in=None):
     r = uv[:, :, :, None, :] - pb.meas[..., 0:2]                              # [N,C,L,W,2]
     w = pb.meas[..., 2:3]
     e = w * r
-    gsc = redescending_dloss(e) * np.sign(e) * w                              # d rho / d slack
-    hsc = irls_weight(e) * w * w
+    if pb.square_loss:
+        gsc = 2.0 * e * w
+        hsc = 2.0 * w * w * np.ones_like(e)
+    else:
+        gsc = redescending_dloss(e) * np.sign(e) * w                          # d rho / d slack
+        hsc = irls_weight(e) * w * w
     # per marker 3x3 / 3 accumulations over cameras and hypotheses
     A = np.einsum("nclwd,ncldi,ncldj->nlij", hsc, P, P)
     b = np.einsum("nclwd,ncldi->nli", gsc, P)

@@ -350,3 +350,34 @@ def test_solve_split_is_bit_identical(gpu):
     torch.cuda.synchronize()
     for k in ("q", "cost", "counters", "c_eq"):
         assert torch.equal(one[k], two[k]), k
+
+
+def test_square_loss_mode_matches_oracle(gpu):
+    """CPE_LOSS_SQUARE = measurement_cost(hand_labeled_data=True): plain (w slack)^2 without the camera multiplier
+    (acinoset_misc.py:471-474); cost and normal equations against the oracle."""
+    import torch
+    from cheetah_pose_estimation_b200 import engine, synthetic
+    from oracle import adapters, cost
+    prob = synthetic.make_problem(S=2, N=7, C=4, seed=47)
+    cams = prob.cams.copy()
+    cams[:, 2:, 20] = 0.6                                                  # must be ignored in this mode
+    batch = engine.Batch.from_numpy(prob.meas, cams, prob.chain_vec, prob.h, loss_mode=engine.LOSS_SQUARE)
+    sv = engine.Solver(gpu, batch)
+    rng = np.random.default_rng(1)
+    q = prob.q_true + rng.normal(0, 0.02, prob.q_true.shape)
+    qd = torch.as_tensor(q, device="cuda:0")
+    out = sv.evaluate(qd)
+    out32 = engine.Solver(gpu, batch, with_solver=False).evaluate(qd, f32=True)["cost"].cpu().numpy()
+    damp = torch.full((2,), 1e-3, dtype=torch.float64, device="cuda:0")
+    Hraw = sv.assemble(qd, damp, raw=True)
+    torch.cuda.synchronize()
+    for s in range(2):
+        pb = adapters.problem_from_arrays(prob.meas[s], cams[s], prob.chain_link, prob.chain_vec[s], prob.h[s],
+                                          square_loss=True)
+        ref = cost.cost_terms(pb, q[s])
+        assert np.allclose(out["cost"][s].cpu().numpy(), ref, rtol=RTOL, atol=1e-9)
+        assert abs(out32[s, 0] - ref[0]) <= RTOL32 * ref[0]
+        H, g = cost.frame_normal_equations(pb, q[s])
+        g = g + cost.motion_gradient(pb, q[s])
+        assert _rel(Hraw[s].cpu().numpy(), H) < RTOL
+        assert _rel(sv.g[s].cpu().numpy(), g) < RTOL

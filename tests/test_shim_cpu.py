@@ -143,3 +143,24 @@ def test_pairwise_pseudo_measurements_follow_the_reference_indexing(tmp_path):
                     got = meas[n - 1, c - 1, l, w - 1]
                     assert got[0] == np.float32(val[0]) and got[1] == np.float32(val[1])
                     assert got[2] == (1.0 if lik > 0.5 else 0.0)
+
+
+def test_hand_labelled_packing(tmp_path):
+    """dlc_hand_labeled arrays hold (x, y) pairs, are not shifted by the sync offset and have likelihood 1
+    (acinoset_misc.py:216-221, 241-242); NaN labels get gate 0 (SURVEY A5 divergence)."""
+    rng = np.random.default_rng(8)
+    arr = [rng.uniform(0, 1000, (12, 50)) for _ in range(2)]
+    arr[1][5, 2 * sk.DLC_INDEX[3]] = np.nan
+    params = misc.TrajectoryParams(str(tmp_path), 2, 9, 7, 0.5, [{"cam": 1, "frame": 1}], True, False, False, False)
+    scene = misc.Scene("", None, None, None, None, None, 90, 2, None)
+    meas, cams = misc.pack_measurements(params, scene, arr)
+    assert meas.shape == (7, 2, 24, 1, 4)
+    for c in range(2):
+        for l, base in enumerate(sk.DLC_INDEX):
+            for n in range(7):
+                x, y = arr[c][n + 2][0::2][base], arr[c][n + 2][1::2][base]
+                if np.isnan(x):
+                    assert meas[n, c, l, 0, 2] == 0.0
+                else:
+                    assert meas[n, c, l, 0, 0] == np.float32(x) and meas[n, c, l, 0, 1] == np.float32(y)
+                    assert meas[n, c, l, 0, 2] == 1.0
