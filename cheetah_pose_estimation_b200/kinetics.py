@@ -1,0 +1,49 @@
+"""Host side of the kinetic path's first slice: rows 0-5 of the equations of motion on the GPU.
+
+Reference: CheetahEstimator.calc_grf_eom / estimate_grf (acinoset_opt.py:120-270): `eom[i](q, dq, ddq, GRFz, GRFxy)`.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib, skeleton
+
+FEET = ("HFL_foot", "HFR_foot", "HBL_foot", "HBR_foot")        # order of pe.foot.feet(robot) (link order)
+N_FORCES, N_PAR = 20, 52
+
+
+def link_params(animal):
+    """par[52] = lengths[17], masses[17], radii[17] in link order, F_scale = total_mass * 9.81
+    (acinoset_opt.py:151-161)."""
+    lengths, radii, masses = skeleton.animal(animal)
+    return np.concatenate([lengths, masses, radii, [float(np.sum(masses)) * 9.81]])
+
+
+def pack_grf(grfz, grfxy):
+    """grf[..., 20] from GRFz[..., 4] and GRFxy[..., 4, 4] (foot-major), the order of eom_vars
+    (acinoset_opt.py:170-171: all Lz first, then the flattened Lx)."""
+    grfz, grfxy = np.asarray(grfz, np.float64), np.asarray(grfxy, np.float64)
+    return np.concatenate([grfz, grfxy.reshape(grfxy.shape[:-2] + (16,))], axis=-1)
+
+
+def eom_rows(q, dq, ddq, grf, par, n_frames=None, device="cuda"):
+    """eom[S,N,6] on the GPU.  q, dq, ddq [S,N,54], grf[S,N,20], par[S,52] (numpy or torch)."""
+    if not torch.cuda.is_available():
+        raise _lib.CpeError("CUDA device required: the hot path has no CPU fallback")
+    lib = _lib.load()
+    dev = torch.device(device)
+    t = [torch.as_tensor(np.ascontiguousarray(a) if isinstance(a, np.ndarray) else a, dtype=torch.float64,
+                         device=dev).contiguous() for a in (q, dq, ddq, grf, par)]
+    S, N = t[0].shape[:2]
+    assert t[0].shape == (S, N, 54) and t[1].shape == (S, N, 54) and t[2].shape == (S, N, 54)
+    assert t[3].shape == (S, N, N_FORCES) and t[4].shape == (S, N_PAR)
+    nf = torch.full((S,), N, dtype=torch.int32, device=dev) if n_frames is None else \
+        torch.as_tensor(n_frames, dtype=torch.int32, device=dev)
+    b = _lib.CpeBatch()
+    b.S, b.N, b.C, b.W = S, N, 0, 1
+    b.n_frames = nf.data_ptr()
+    out = torch.zeros(S, N, 6, dtype=torch.float64, device=dev)
+    _lib.check(lib.cpe_eom_f64(C.byref(b), *[C.c_void_p(x.data_ptr()) for x in t], C.c_void_p(out.data_ptr()),
+                               C.c_void_p(torch.cuda.current_stream().cuda_stream)), "cpe_eom_f64")
+    return out

@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 108          /* 0.1.8 */
+#define CPE_VERSION 109          /* 0.1.9 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -264,6 +264,17 @@ int cpe_update_multipliers_f64(const cpe_model *model, const cpe_batch *batch, c
 int cpe_eval_host_f64(const cpe_model *model, const cpe_batch *batch_dev, const double *h_q, const void *h_meas,
                       double *d_q, void *d_meas, const cpe_eval_out *out_dev, double *d_cost, double *h_cost,
                       double *h_resid, void *stream);
+
+/* Kinetic path, first slice: rows 0-5 of the equations of motion M ddq + C + G - B F, the functions
+ * eom[i](q, dq, ddq, GRFz, GRFxy) of CheetahEstimator.calc_grf_eom / estimate_grf (acinoset_opt.py:120-270).
+ * q, dq, ddq [S,N,54]; grf[S,N,20] = GRFz of the feet HFL, HFR, HBL, HBR, then GRFxy[foot][4], in units of
+ * F_scale (acinoset_opt.py:142-149); link_par[S,52] = lengths[17], masses[17], radii[17] in link order, then
+ * F_scale = total_mass * 9.81; eom[S,N,6].  The generated code carries the trunk dimensions of `jules` / `phantom` in
+ * its hip offsets, exactly as the reference bakes them (cheetah.py:32-38). */
+#define CPE_EOM_N_FORCES 20
+#define CPE_EOM_N_PAR 52
+int cpe_eom_f64(const cpe_batch *batch, const double *q, const double *dq, const double *ddq, const double *grf,
+                const double *link_par, double *eom, void *stream);
 
 #ifdef __cplusplus
 }
