@@ -47,3 +47,39 @@ def eom_rows(q, dq, ddq, grf, par, n_frames=None, device="cuda"):
     _lib.check(lib.cpe_eom_f64(C.byref(b), *[C.c_void_p(x.data_ptr()) for x in t], C.c_void_p(out.data_ptr()),
                                C.c_void_p(torch.cuda.current_stream().cuda_stream)), "cpe_eom_f64")
     return out
+
+
+def estimate_grf(q, dq, ddq, par, contact, n_frames=None, iters=600, device="cuda"):
+    """Per-frame GRF estimate of CheetahEstimator.estimate_grf (acinoset_opt.py:176-249) for S sequences at once.
+
+    q, dq, ddq [S,N,54]; par[S,52]; contact[S,N,4] (non-zero = foot on the ground, feet in `FEET` order).
+    Returns (grf[S,N,20] in units of F_scale, resid[S,N] = the minimal ||eom||).  The reference runs one IPOPT solve per
+    frame (:204-249); here `cpe_eom_affine_f64` splits the rows into a - Bm F and `cpe_grf_solve_f64` solves every
+    frame's bounded least-squares problem in one launch."""
+    if not torch.cuda.is_available():
+        raise _lib.CpeError("CUDA device required: the hot path has no CPU fallback")
+    lib = _lib.load()
+    dev = torch.device(device)
+    t = [torch.as_tensor(np.ascontiguousarray(a) if isinstance(a, np.ndarray) else a, dtype=torch.float64,
+                         device=dev).contiguous() for a in (q, dq, ddq, par)]
+    S, N = t[0].shape[:2]
+    assert all(x.shape == (S, N, 54) for x in t[:3]) and t[3].shape == (S, N_PAR)
+    ct = torch.as_tensor(np.asarray(contact) != 0 if not torch.is_tensor(contact) else contact != 0, device=dev)
+    ct = ct.to(torch.int32).contiguous()
+    assert ct.shape == (S, N, 4)
+    nf = torch.full((S,), N, dtype=torch.int32, device=dev) if n_frames is None else \
+        torch.as_tensor(n_frames, dtype=torch.int32, device=dev)
+    b = _lib.CpeBatch()
+    b.S, b.N, b.C, b.W = S, N, 0, 1
+    b.n_frames = nf.data_ptr()
+    a = torch.zeros(S, N, 6, dtype=torch.float64, device=dev)
+    Bm = torch.zeros(S, N, 6, N_FORCES, dtype=torch.float64, device=dev)
+    grf = torch.zeros(S, N, N_FORCES, dtype=torch.float64, device=dev)
+    resid = torch.zeros(S, N, dtype=torch.float64, device=dev)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    p = lambda x: C.c_void_p(x.data_ptr())
+    _lib.check(lib.cpe_eom_affine_f64(C.byref(b), p(t[0]), p(t[1]), p(t[2]), p(t[3]), p(a), p(Bm), st),
+               "cpe_eom_affine_f64")
+    _lib.check(lib.cpe_grf_solve_f64(C.byref(b), p(a), p(Bm), p(ct), int(iters), p(grf), p(resid), st),
+               "cpe_grf_solve_f64")
+    return grf, resid

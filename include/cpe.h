@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 109          /* 0.1.9 */
+#define CPE_VERSION 110          /* 0.1.10 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -275,6 +275,15 @@ int cpe_eval_host_f64(const cpe_model *model, const cpe_batch *batch_dev, const 
 #define CPE_EOM_N_PAR 52
 int cpe_eom_f64(const cpe_batch *batch, const double *q, const double *dq, const double *ddq, const double *grf,
                 const double *link_par, double *eom, void *stream);
+/* The rows are affine in the forces: eom = a - Bm grf.  a[S,N,6], Bm[S,N,6,20]. */
+int cpe_eom_affine_f64(const cpe_batch *batch, const double *q, const double *dq, const double *ddq,
+                       const double *link_par, double *a, double *Bm, void *stream);
+/* Per-frame GRF estimate of CheetahEstimator.estimate_grf (acinoset_opt.py:176-249): minimise || a - Bm F || over
+ * 0 <= F <= 5 with the friction polyhedron 1.3 GRFz[f] >= sum_i GRFxy[f][i] (:187-190); contact[S,N,4] != 0 marks the
+ * feet on the ground, the forces of the others are fixed to 0 (:221-229).  Accelerated projected gradient with adaptive
+ * restart, `iters` iterations (600 reaches the optimum value to ~1e-14 ||a|| on the fixture).  grf[S,N,20], resid[S,N] = the optimal || eom ||. */
+int cpe_grf_solve_f64(const cpe_batch *batch, const double *a, const double *Bm, const int32_t *contact, int32_t iters,
+                      double *grf, double *resid, void *stream);
 
 #ifdef __cplusplus
 }

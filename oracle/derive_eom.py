@@ -116,6 +116,23 @@ def emit_cuda(rows, inputs, path):
         lines.append(f"    const double {sym.name} = {pr.doprint(e)};")
     for i, e in enumerate(red):
         lines.append(f"    out[{i}] = {pr.doprint(e)};")
+    lines += ["}", ""]
+    # the rows are affine in the forces: row_i = a_i - sum_j Bm[i][j] F[j]; Bm depends on q and par only
+    Fs = [sp.Symbol(f"F[{j}]") for j in range(20)]
+    rs = [r.xreplace(sub) for r in rows]
+    Bm = [[-sp.diff(rs[i], Fs[j]) for j in range(20)] for i in range(6)]
+    for i in range(6):
+        for j in range(20):
+            assert not (Bm[i][j].free_symbols & set(Fs))
+    repl2, red2 = sp.cse([Bm[i][j] for i in range(6) for j in range(20)], symbols=sp.numbered_symbols("b"), order="none")
+    print(f"force matrix: {len(repl2)} temporaries")
+    lines += ["// Bm[6][20] with  row_i = a_i - sum_j Bm[i][j] F[j]  (generalised forces of the feet: foot.py:393-397).",
+              "__device__ __noinline__ void eom_force_matrix(const double *__restrict__ q, const double *__restrict__ par,",
+              "                                              double *__restrict__ Bm) {"]
+    for sym, e in repl2:
+        lines.append(f"    const double {sym.name} = {pr.doprint(e)};")
+    for i, e in enumerate(red2):
+        lines.append(f"    Bm[{i}] = {pr.doprint(e)};")
     lines += ["}", "}  // namespace cpe", ""]
     with open(path, "w") as f:
         f.write("\n".join(lines))
@@ -138,7 +155,15 @@ def golden(rows, inputs, values, path, n=24, seed=11):
     pars = np.tile(par, (n, 1))
     pars[n // 2:, :17] *= rng.uniform(0.9, 1.1, (n - n // 2, 17))             # other animals: perturbed link lengths
     out = np.array([fn(*np.concatenate([q[i], dq[i], ddq[i], F[i], pars[i]])) for i in range(n)], dtype=float)
-    np.savez_compressed(path, q=q, dq=dq, ddq=ddq, F=F, par=pars, eom=out, feet=np.array(values["feet"]))
+    # affine split  row = a - Bm F : a = rows at F = 0, column j of Bm = a - rows at F = e_j (same lambdified functions)
+    a = np.array([fn(*np.concatenate([q[i], dq[i], ddq[i], 0 * F[i], pars[i]])) for i in range(n)], dtype=float)
+    Bm = np.zeros((n, 6, 20))
+    for j in range(20):
+        e = np.zeros(20)
+        e[j] = 1.0
+        Bm[:, :, j] = a - np.array([fn(*np.concatenate([q[i], dq[i], ddq[i], e, pars[i]])) for i in range(n)], dtype=float)
+    assert np.abs(a - np.einsum("nij,nj->ni", Bm, F) - out).max() < 1e-8 * np.abs(out).max()
+    np.savez_compressed(path, q=q, dq=dq, ddq=ddq, F=F, par=pars, eom=out, a=a, Bm=Bm, feet=np.array(values["feet"]))
     print("golden eom rows, first frame:", out[0])
 
 
