@@ -83,3 +83,32 @@ def estimate_grf(q, dq, ddq, par, contact, n_frames=None, iters=600, device="cud
     _lib.check(lib.cpe_grf_solve_f64(C.byref(b), p(a), p(Bm), p(ct), int(iters), p(grf), p(resid), st),
                "cpe_grf_solve_f64")
     return grf, resid
+
+
+def contact_mask(metadata):
+    """contact[N,4] from an `autogen-contact.json` dict: N = end_frame - start_frame, foot f is on the ground at row fe
+    when start_frame + fe lies in one of its [first, last) ranges (acinoset_opt.py:203-229; entries of a foot may be
+    null, extra fields after the two frame numbers are ignored as the reference does)."""
+    start, end = int(metadata["start_frame"]), int(metadata["end_frame"])
+    order = metadata["contacts"]
+    out = np.zeros((max(end - start, 0), 4), dtype=np.int32)
+    for f, name in enumerate(FEET):
+        for seq in (order.get(name) or []):
+            lo, hi = max(int(seq[0]) - start, 0), min(int(seq[1]) - start, out.shape[0])
+            if hi > lo:
+                out[lo:hi, f] = 1
+    return out
+
+
+def estimate_grf_states(fte_states, metadata, animal, iters=600, device="cuda"):
+    """CheetahEstimator.estimate_grf (acinoset_opt.py:176-268) for one trajectory: `fte_states` is the dict of a saved
+    fte.pickle (q, dq, ddq [>=N,54]), `metadata` the contact JSON.  Returns (grfz_est, grfxy_est): per foot name a list
+    over the N frames of GRFz and of the 4 GRFxy values -- the reference's return value."""
+    ct = contact_mask(metadata)
+    N = ct.shape[0]
+    q, dq, ddq = (np.asarray(fte_states[k], np.float64)[None, :N] for k in ("q", "dq", "ddq"))
+    grf, _ = estimate_grf(q, dq, ddq, link_params(animal)[None], ct[None], iters=iters, device=device)
+    F = grf[0].cpu().numpy()
+    grfz_est = {name: [float(v) for v in F[:, f]] for f, name in enumerate(FEET)}
+    grfxy_est = {name: [[float(v) for v in row] for row in F[:, 4 + 4 * f:8 + 4 * f]] for f, name in enumerate(FEET)}
+    return grfz_est, grfxy_est

@@ -65,6 +65,48 @@ def test_grf_oracle_is_feasible_and_not_worse_than_zero(golden_dir):
                 assert F[f] == 0 and not F[4 + 4 * f:8 + 4 * f].any()
 
 
+META = {"start_frame": 53, "end_frame": 83,
+        "contacts": {"HFL_foot": [[58, 64, 0, "leading"]], "HFR_foot": [[54, 60, 1, "trailing"]],
+                     "HBL_foot": [[69, 75, 2, "trailing"], [80, 90, 2, "x"]], "HBR_foot": None}}
+
+
+def test_contact_mask_follows_the_reference_ranges():
+    from cheetah_pose_estimation_b200 import kinetics
+    m = kinetics.contact_mask(META)
+    assert m.shape == (30, 4)
+    for fe in range(30):                                   # literal restatement of acinoset_opt.py:221-229
+        for f, name in enumerate(kinetics.FEET):
+            on = False
+            seqs = META["contacts"].get(name)
+            if seqs is not None:
+                idx = []
+                for s in seqs:
+                    idx = idx + list(range(s[0], s[1]))
+                on = (53 + fe) in idx
+            assert bool(m[fe, f]) == on, (fe, name)
+
+
+@pytest.mark.gpu
+def test_estimate_grf_states_reference_return_shape(golden_dir):
+    from cheetah_pose_estimation_b200 import kinetics
+    from oracle import grf as ogrf
+    g = np.load(os.path.join(golden_dir, "eom_ref.npz"))
+    n = 30
+    rep = lambda a: np.concatenate([a] * (n // a.shape[0] + 1))[:n + 2]
+    st = {"q": rep(g["q"]), "dq": rep(g["dq"]), "ddq": rep(g["ddq"])}
+    gz, gxy = kinetics.estimate_grf_states(st, META, "jules")
+    assert set(gz) == set(kinetics.FEET) and all(len(v) == n for v in gz.values())
+    assert all(len(v) == n and len(v[0]) == 4 for v in gxy.values())
+    m = kinetics.contact_mask(META)
+    assert not any(gz["HBR_foot"]) and all(gz["HFL_foot"][fe] == 0 for fe in range(n) if not m[fe, 0])
+    assert not any(any(gz[f][fe] for f in kinetics.FEET) for fe in range(n) if not m[fe].any())   # :231-236
+    fe = 6                                                  # frame 59: both front feet down
+    F = np.array([gz[f][fe] for f in kinetics.FEET] + [v for f in kinetics.FEET for v in gxy[f][fe]])
+    i = fe % g["q"].shape[0]
+    _, ro = ogrf.solve_frame(g["a"][i], g["Bm"][i], m[fe])
+    assert abs(np.linalg.norm(g["a"][i] - g["Bm"][i] @ F) - ro) <= 1e-9 * np.linalg.norm(g["a"][i])
+
+
 @pytest.mark.gpu
 def test_grf_estimate_matches_oracle_value(golden_dir):
     """Optimal VALUE parity (the minimiser is not unique): | r_gpu - r_oracle | <= 1e-9 ||a|| and never below the oracle's
