@@ -49,6 +49,8 @@ def parse_args():
     ap.add_argument("--lm-seqs", type=int, default=444, help="sequences of the LM-solve leg (0 = skip)")
     ap.add_argument("--lm-iters", type=int, default=20)
     ap.add_argument("--lm-split", type=int, default=1, help="sub-batches of the LM leg solved on separate streams")
+    ap.add_argument("--mono-seqs", type=int, default=60, help="monocular hypotheses of the config-3 leg (0 = skip)")
+    ap.add_argument("--grf-seqs", type=int, default=444, help="sequences of the GRF-estimate leg (0 = skip)")
     ap.add_argument("--cpu-seqs", type=int, default=64, help="sequences of the cpu_baseline sample (0 = skip)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-f32", action="store_true", help="skip the FP32-flavour leg")
@@ -347,6 +349,83 @@ def lm_leg(a, r):
             "settings": {"n_outer": 3, "max_iter": a.lm_iters, "ftol": 1e-6}}
 
 
+def monocular_leg(a, r):
+    """BASELINE config 3 in shape: S monocular hypotheses (C = 1), 100 frames, data-driven priors on.  The priors are
+    FITTED HERE (CPU, scikit-learn, outside the timed region -- as in the reference) on the reduced poses of the
+    synthetic trajectories: GaussianMixture(5) on the 22 joint entries and a linear AR(4) model."""
+    import numpy as np
+    import torch
+    from sklearn.linear_model import LinearRegression
+    from sklearn.mixture import GaussianMixture
+    from cheetah_pose_estimation_b200 import acinoset_models, engine, priors, skeleton, synthetic
+    S = a.mono_seqs
+    if S <= 0:
+        return None
+    N = 100
+    dev = r["dev"]
+    batch, q_true, q_init = synthetic.make_device_problem(S, N, 1, seed=a.seed + 77 + 1000 * r["rank"], device=dev,
+                                                          dlc_native=True)
+    ind = skeleton.independent_coords()
+    X = q_true.cpu().numpy()[:, :, ind] @ priors.reduced_matrix().T               # [S,N,28]
+    gmm = GaussianMixture(n_components=5, random_state=42, max_iter=2000, reg_covar=1e-4).fit(X[:, :, 6:].reshape(-1, 22))
+    xy = np.concatenate([acinoset_models.series_to_supervised(x, 4) for x in X])
+    lr = LinearRegression().fit(xy[:, :112], xy[:, 112:])
+
+    class _M:
+        coef_, intercept_ = lr.coef_, lr.intercept_
+        error_variance = np.var(xy[:, 112:] - lr.predict(xy[:, :112]), axis=0)
+    P = priors.Priors(acinoset_models.pack_priors(gmm, _M), dev)
+    q0 = q_init.contiguous()
+    sv = engine.Solver(r["model"], batch, priors=P)
+    sv.solve(q0, max_iter=2, n_outer=1)
+    l0 = sv.launches
+    r["barrier"]()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    res = sv.solve(q0, max_iter=a.lm_iters, n_outer=3)
+    e1.record()
+    r["barrier"]()
+    ms = e0.elapsed_time(e1)
+    err = (res["q"][:, :, :3] - q_true[:, :, :3]).norm(dim=-1)
+    return {"sequences": S, "frames": N, "cams": 1, "sequences_per_s": S / (ms * 1e-3), "ms": ms,
+            "lockstep_iterations": res["lockstep_iterations"], "launches": sv.launches - l0,
+            "final_cost_mean": float(res["cost"][:, :2].sum(dim=1).mean()),
+            "prior_cost_mean": res["prior_cost"].mean(dim=0).tolist(),
+            "base_position_error_m_median": float(err.median()),
+            "max_abs_joint_violation": float(res["c_eq"].abs().max()), "failed_pivots": int(res["status"].sum()),
+            "priors": "GMM(5) pose prior + AR(4) motion prior fitted on the synthetic trajectories (CPU, untimed)"}
+
+
+def grf_leg(a, r):
+    """Per-frame GRF estimate (cpe_eom_affine_f64 + cpe_grf_solve_f64) on the LM leg's trajectories: frames/s."""
+    import numpy as np
+    import torch
+    from cheetah_pose_estimation_b200 import kinetics
+    S = min(a.grf_seqs, r["batch"].S)
+    if S <= 0:
+        return None
+    q = r["q"][:S].contiguous()
+    N = q.shape[1]
+    h = 1.0 / 120.0
+    dq = torch.zeros_like(q)
+    dq[:, 1:] = (q[:, 1:] - q[:, :-1]) / h
+    ddq = torch.zeros_like(q)
+    ddq[:, 1:] = (dq[:, 1:] - dq[:, :-1]) / h
+    rng = np.random.default_rng(a.seed + 5)
+    ct = torch.as_tensor(rng.integers(0, 2, (S, N, 4)), device=r["dev"])
+    par = np.tile(kinetics.link_params("jules")[None], (S, 1))
+    kinetics.estimate_grf(q, dq, ddq, par, ct, device=r["dev"])
+    r["barrier"]()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    grf, resid = kinetics.estimate_grf(q, dq, ddq, par, ct, device=r["dev"])
+    e1.record()
+    r["barrier"]()
+    ms = e0.elapsed_time(e1)
+    return {"sequences": S, "frames": S * N, "frames_per_s": S * N / (ms * 1e-3), "ms": ms, "iterations": 600,
+            "launches": 2, "resid_mean": float(resid.mean()), "grf_max": float(grf.max())}
+
+
 def cpu_baseline_leg(a):
     if a.cpu_seqs <= 0:
         return None
@@ -388,6 +467,8 @@ def main():
         lm["ms"] = sharding.reduce_max(lm["ms"], r["dev"])
         lm["sequences"] *= world
         lm["sequences_per_s"] = lm["sequences"] / (lm["ms"] * 1e-3)
+    mono = monocular_leg(a, r) if world == 1 else None
+    grf = grf_leg(a, r) if world == 1 else None
     if rank == 0:
         fv_rank = a.seqs * a.frames * a.cams
         fv_total = fv_rank * world
@@ -435,6 +516,10 @@ def main():
                            "api": "cpe_eval_f32 (scaled FP32 residual path; residuals/Jacobian in float, FK and cost sums FP64)"}
         if lm is not None:
             line["lm"] = lm
+        if mono is not None:
+            line["monocular"] = mono
+        if grf is not None:
+            line["grf"] = grf
         if world == 1:
             line["cpu_baseline"] = cpu_baseline_leg(a)
         print(json.dumps(line), flush=True)

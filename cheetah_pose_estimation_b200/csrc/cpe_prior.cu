@@ -365,6 +365,233 @@ __global__ void __launch_bounds__(256) band_general_kernel(const __grid_constant
     if (tid == 0 && p.status) p.status[s] = bad;
 }
 
+// ---- blocked variant: the band is a whole number of 28-wide frame blocks (always the case for the monocular path: ----
+// half-bandwidth = max(window, 3) frames).  One frame = one panel:
+//   A  warp 0 factorises the 28x28 diagonal block in registers (lane = row, shuffles broadcast the pivot column);
+//   B  one thread per panel row solves X L_kk^T = A_panel (right-looking, L_kk broadcast from shared memory); the
+//      right-hand side is one more row, so the forward substitution rides along;
+//   C  7x7 register tiles apply the rank-28 update to the lower part of the trailing window;
+//   D  the ring slot of frame k takes the rows of frame k + R.
+// Three barriers per frame instead of two per scalar column (56 per frame) in band_general_kernel.  The backward
+// substitution streams the column panels of L back through a double buffer in shared memory.
+constexpr int LDP = 29;
+
+// Column J of the in-register Cholesky (lane i holds row i).  A template recursion instead of `#pragma unroll`: nvcc
+// leaves the triangular double loop partly rolled, which puts the row into local memory.
+template <int J>
+__device__ __forceinline__ void chol_column(double (&a)[NX], int i, double *idg, int *bad) {
+    const unsigned FULL = 0xffffffffu;
+    double ajj = __shfl_sync(FULL, a[J], J);
+    if (!(ajj > 0.0)) { ajj = 1.0; if (i == 0) *bad = 1; }
+    const double d = sqrt(ajj), id = 1.0 / d;
+    a[J] = (i == J) ? d : a[J] * id;
+    if (i == J) idg[J] = id;
+#pragma unroll
+    for (int c = J + 1; c < NX; ++c) {
+        const double lc = __shfl_sync(FULL, a[J], c);
+        if (i >= c) a[c] -= a[J] * lc;
+    }
+    if constexpr (J + 1 < NX) chol_column<J + 1>(a, i, idg, bad);
+}
+
+// Row-wise solve x L^T = a against LdT[t * 28 + c] = L[c][t] (right-looking), same reason for the recursion.
+template <int T>
+__device__ __forceinline__ void panel_column(double (&a)[NX], const double *LdT, const double *idg) {
+    const double x = a[T] * idg[T];
+    a[T] = x;
+#pragma unroll
+    for (int c = T + 1; c < NX; ++c) a[c] -= x * LdT[T * NX + c];
+    if constexpr (T + 1 < NX) panel_column<T + 1>(a, LdT, idg);
+}
+
+__global__ void __launch_bounds__(256) band_block_kernel(const __grid_constant__ BandParams p) {
+    extern __shared__ __align__(16) double smg[];
+    const int tid = threadIdx.x, lane = tid & 31;
+    const unsigned FULL = 0xffffffffu;
+    const int s = blockIdx.x;
+    const int N = p.b.N, WN = p.bw + 1, R = WN / NX, nbk = R - 1, LD = WN + 1;
+    const int nf = p.b.n_frames[s];
+    if (p.b.active && !p.b.active[s]) return;
+    double *Wn = smg;                       // [WN][LD] ring window: frame f lives in slot f % R
+    double *Lp = Wn + WN * LD;              // [112][LDP] panel of the current frame
+    double *LdT = Lp + 112 * LDP;           // [28][28]  L_kk transposed: LdT[t * 28 + c] = L_kk[c][t]
+    double *idg = LdT + NX * NX;            // [32] 1 / diag(L_kk)
+    double *bv = idg + 32;                  // [160] right-hand-side ring / backward solution ring
+    double *zk = bv + 160;                  // [2][32]
+    __shared__ int bad;
+    if (tid == 0) bad = 0;
+    const double *Sg = p.S + (size_t)s * N * NX * NX;
+    const double *gh = p.ghat + (size_t)s * N * NX;
+    const double *Mb = p.Mband + (size_t)s * p.mstride;
+    double *Lb = p.Lband + (size_t)s * N * NX * WN;
+    double *dl = p.delta + (size_t)s * N * NX;
+    // rows of frame f (lower part: column frames f - nbk .. f) into its ring slot
+    auto load_frame = [&](int f) {
+        const int sf = (f % R) * NX;
+        for (int e = tid; e < NX * WN; e += 256) {
+            const int r = e / WN, cc = e - r * WN;
+            const int g = f - nbk + cc / NX, c = cc % NX;
+            if (g < 0 || (g == f && c > r)) continue;
+            const int i = f * NX + r, col = g * NX + c;
+            double v = Mb[(size_t)i * WN + (i - col)];
+            if (g == f) v += Sg[(size_t)f * NX * NX + r * NX + c];
+            Wn[(sf + r) * LD + (g % R) * NX + c] = v;
+        }
+        if (tid < NX) bv[sf + tid] = -gh[(size_t)f * NX + tid];
+    };
+    for (int f = 0; f < min(R, nf); ++f) load_frame(f);
+    __syncthreads();
+
+    for (int k = 0; k < nf; ++k) {
+        const int m = min(nbk, nf - 1 - k);
+        const int s0 = (k % R) * NX;
+        // ---- A: Cholesky of the diagonal block ----------------------------------------------------------------------
+        if (tid < 32) {
+            const int i = lane;
+            double a[NX];
+            {
+                // the part above the diagonal is stale shared memory: it is loaded but never feeds a lower entry
+                const double *row = Wn + (s0 + (i < NX ? i : NX - 1)) * LD + s0;
+#pragma unroll
+                for (int c = 0; c < NX; ++c) a[c] = row[c];
+            }
+            chol_column<0>(a, i, idg, &bad);
+            if (i < NX) {
+#pragma unroll
+                for (int t = 0; t < NX; ++t) LdT[t * NX + i] = a[t];      // entries with t > i are never read
+            }
+        }
+        __syncthreads();
+        // in-block part of the columns of L to HBM (threads that have no panel row)
+        if (tid >= 128) {
+            for (int e = tid - 128; e < NX * NX; e += 128) {
+                const int t = e / NX, i = e - t * NX;
+                if (i >= t) Lb[(size_t)(k * NX + t) * WN + (i - t)] = LdT[e];
+            }
+        }
+        // ---- B: panel rows (and the right-hand side as row 112) --------------------------------------------------------
+        if (tid < NX * m || tid == 112) {
+            const bool rhs = tid == 112;
+            const double *src = rhs ? bv + s0 : Wn + ((((k + 1 + tid / NX) % R) * NX + tid % NX) * LD + s0);
+            double a[NX];
+#pragma unroll
+            for (int t = 0; t < NX; ++t) a[t] = src[t];
+            panel_column<0>(a, LdT, idg);
+            if (rhs) {
+#pragma unroll
+                for (int t = 0; t < NX; ++t) { zk[t] = a[t]; dl[(size_t)k * NX + t] = a[t]; }
+            } else {
+#pragma unroll
+                for (int t = 0; t < NX; ++t) {
+                    Lp[tid * LDP + t] = a[t];
+                    Lb[(size_t)(k * NX + t) * WN + (NX - t + tid)] = a[t];
+                }
+            }
+        }
+        __syncthreads();
+        // ---- C: trailing update (lower 7x7 tiles) + right-hand side ------------------------------------------------------
+        {
+            const int ty = tid >> 4, tx = tid & 15;
+            if (ty >= tx && 7 * ty < NX * m) {
+                double acc[7][7];
+#pragma unroll
+                for (int i = 0; i < 7; ++i)
+#pragma unroll
+                    for (int j = 0; j < 7; ++j) acc[i][j] = 0.0;
+                const double *lr = Lp + 7 * ty * LDP, *lc = Lp + 7 * tx * LDP;
+#pragma unroll 4
+                for (int t = 0; t < NX; ++t) {
+                    double xr[7], xc[7];
+#pragma unroll
+                    for (int i = 0; i < 7; ++i) { xr[i] = lr[i * LDP + t]; xc[i] = lc[i * LDP + t]; }
+#pragma unroll
+                    for (int i = 0; i < 7; ++i)
+#pragma unroll
+                        for (int j = 0; j < 7; ++j) acc[i][j] += xr[i] * xc[j];
+                }
+                const int prow = ((k + 1 + (7 * ty) / NX) % R) * NX + (7 * ty) % NX;
+                const int pcol = ((k + 1 + (7 * tx) / NX) % R) * NX + (7 * tx) % NX;
+#pragma unroll
+                for (int i = 0; i < 7; ++i)
+#pragma unroll
+                    for (int j = 0; j < 7; ++j) Wn[(prow + i) * LD + pcol + j] -= acc[i][j];
+            }
+            if (tid < NX * m) {
+                double acc = 0.0;
+#pragma unroll
+                for (int t = 0; t < NX; ++t) acc += Lp[tid * LDP + t] * zk[t];
+                bv[((k + 1 + tid / NX) % R) * NX + tid % NX] -= acc;
+            }
+        }
+        // ---- D: the freed slot takes frame k + R ---------------------------------------------------------------------
+        if (k + R < nf) load_frame(k + R);
+        __syncthreads();
+    }
+    // ---- backward substitution L^T delta = z, one frame per step ---------------------------------------------------------
+    // The raw column panel of frame k (28 columns x WN entries, contiguous in Lband) is staged in shared memory; the panel
+    // of frame k - 1 is fetched into registers meanwhile.  bv becomes the ring of the last R solutions.
+    double *P0 = Wn, *P1 = Wn + NX * WN, *accv = LdT;
+    const int np = NX * WN;
+    if (nf > 0) {
+        const double *src = Lb + (size_t)(nf - 1) * np;
+        double *dst = ((nf - 1) & 1) ? P1 : P0;
+        for (int e = tid; e < np; e += 256) dst[e] = src[e];
+        if (tid < NX) zk[((nf - 1) & 1) * 32 + tid] = dl[(size_t)(nf - 1) * NX + tid];
+    }
+    __syncthreads();
+    for (int k = nf - 1; k >= 0; --k) {
+        const double *cur = (k & 1) ? P1 : P0;
+        double *nxt = (k & 1) ? P0 : P1;
+        const int m = min(nbk, nf - 1 - k);
+        double pre[16], zpre = 0.0;
+        if (k > 0) {
+            const double *src = Lb + (size_t)(k - 1) * np;
+#pragma unroll
+            for (int e = 0; e < 16; ++e) pre[e] = (tid + 256 * e < np) ? src[tid + 256 * e] : 0.0;
+            if (tid < NX) zpre = dl[(size_t)(k - 1) * NX + tid];
+        }
+        // step 1: contributions of the later frames, 8 threads per column
+        {
+            const int c = tid >> 3, g = tid & 7;
+            double part = 0.0;
+            if (c < NX) {
+                const double *col = cur + c * WN - c;                   // col[u] = L(frame row u, column c), u >= c
+                for (int u = NX + g; u < NX * (m + 1); u += 8)
+                    part += col[u] * bv[((k + u / NX) % R) * NX + u % NX];
+            }
+            part += __shfl_xor_sync(FULL, part, 1);
+            part += __shfl_xor_sync(FULL, part, 2);
+            part += __shfl_xor_sync(FULL, part, 4);
+            if (c < NX && g == 0) accv[c] = zk[(k & 1) * 32 + c] - part;
+        }
+        __syncthreads();
+        // step 2: triangular solve with L_kk^T (warp 0) while the other warps park the prefetched panel
+        if (tid < 32) {
+            const int c1 = lane < NX ? lane : 0;
+            double v = lane < NX ? accv[lane] : 0.0;
+            const double inv = 1.0 / cur[c1 * WN];
+            for (int c = NX - 1; c >= 0; --c) {
+                if (lane == c) v *= inv;
+                const double dcur = __shfl_sync(FULL, v, c);
+                if (lane < c) v -= cur[lane * WN + (c - lane)] * dcur;
+            }
+            if (lane < NX) {
+                bv[(k % R) * NX + lane] = v;
+                dl[(size_t)k * NX + lane] = v;
+            }
+        }
+        if (k > 0) {
+#pragma unroll
+            for (int e = 0; e < 16; ++e)
+                if (tid + 256 * e < np) nxt[tid + 256 * e] = pre[e];
+            if (tid < NX) zk[((k - 1) & 1) * 32 + tid] = zpre;
+        }
+        __syncthreads();
+    }
+    for (int i = nf * NX + tid; i < N * NX; i += 256) dl[i] = 0.0;
+    if (tid == 0 && p.status) p.status[s] = bad;
+}
+
 }  // namespace cpe
 
 extern "C" int cpe_band_solve_general_f64(const cpe_batch *b, const double *Sblk, const double *ghat, const double *Mband,
@@ -376,6 +603,14 @@ extern "C" int cpe_band_solve_general_f64(const cpe_batch *b, const double *Sblk
     p.b = *b; p.S = Sblk; p.ghat = ghat; p.Mband = Mband; p.mstride = mband_stride; p.bw = bw; p.Lband = Lband;
     p.delta = delta_ind; p.status = status;
     const int WN = bw + 1;
+    if (WN % cpe::NX == 0 && WN / cpe::NX >= 2 && WN / cpe::NX <= 5) {
+        // whole frame blocks: blocked factorisation (3 barriers per frame)
+        const size_t smb = (size_t)(WN * (WN + 1) + 112 * cpe::LDP + cpe::NX * cpe::NX + 32 + 160 + 64) * sizeof(double);
+        cudaError_t eb = cudaFuncSetAttribute(cpe::band_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smb);
+        if (eb != cudaSuccess) return (int)eb;
+        cpe::band_block_kernel<<<b->S, 256, smb, (cudaStream_t)stream>>>(p);
+        return (int)cudaGetLastError();
+    }
     const size_t smem = (size_t)(WN * WN + 3 * WN) * sizeof(double);
     if (smem > 227 * 1024) return CPE_E_DIM;
     cudaError_t e = cudaFuncSetAttribute(cpe::band_general_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -2,7 +2,7 @@
 # usage (on the GPU box): bash scripts/ncu_profile.sh <tag>
 set -x
 TAG=${1:-rX}
-CMD="python bench.py --no-f32 --seqs 64 --wave 32 --lm-seqs 16 --lm-iters 4 --cpu-seqs 0 --steps 2 --warmup 1 --no-e2e"
+CMD="python bench.py --no-f32 --mono-seqs 0 --grf-seqs 0 --seqs 64 --wave 32 --lm-seqs 16 --lm-iters 4 --cpu-seqs 0 --steps 2 --warmup 1 --no-e2e"
 K="eval_kernel|assemble_kernel|band_solve|step_apply|reduce_cost|step_accept|update_multipliers"
 $CMD > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"$K" -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/ncu1.log 2>&1
