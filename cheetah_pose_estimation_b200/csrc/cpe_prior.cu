@@ -366,24 +366,27 @@ __global__ void __launch_bounds__(256) band_general_kernel(const __grid_constant
 }
 
 // ---- blocked variant: the band is a whole number of 28-wide frame blocks (always the case for the monocular path: ----
-// half-bandwidth = max(window, 3) frames).  One frame = one panel:
-//   A  warp 0 factorises the 28x28 diagonal block in registers (lane = row, shuffles broadcast the pivot column);
-//   B  one thread per panel row solves X L_kk^T = A_panel (right-looking, L_kk broadcast from shared memory); the
-//      right-hand side is one more row, so the forward substitution rides along;
-//   C  7x7 register tiles apply the rank-28 update to the lower part of the trailing window;
-//   D  the ring slot of frame k takes the rows of frame k + R.
-// Three barriers per frame instead of two per scalar column (56 per frame) in band_general_kernel.  The backward
-// substitution streams the column panels of L back through a double buffer in shared memory.
+// half-bandwidth = max(window, 3) frames).  One frame = one panel, two barriers per frame:
+//   B      one thread per panel row solves X L_kk^T = A_panel (right-looking, L_kk broadcast from shared memory); the
+//          right-hand side is one more row, so the forward substitution rides along;
+//   A | C  warp 0 applies the panel to the NEXT diagonal block in registers (lane = row) and factorises it with shuffle
+//          broadcasts of the pivot column, while warps 1-7 apply the rank-28 update to the rest of the lower window
+//          in 7x7 register tiles and move the rows of frame k + R (fetched into registers before B) into the ring
+//          slot frame k frees.
+// band_general_kernel needs two barriers per scalar column (56 per frame).  The backward substitution streams the
+// column panels of L back through a double buffer in shared memory.
 constexpr int LDP = 29;
 
 // Column J of the in-register Cholesky (lane i holds row i).  A template recursion instead of `#pragma unroll`: nvcc
 // leaves the triangular double loop partly rolled, which puts the row into local memory.
 template <int J>
-__device__ __forceinline__ void chol_column(double (&a)[NX], int i, double *idg, int *bad) {
+__device__ __forceinline__ void chol_column(double (&a)[NX], int i, double *idg, int &bad) {
     const unsigned FULL = 0xffffffffu;
     double ajj = __shfl_sync(FULL, a[J], J);
-    if (!(ajj > 0.0)) { ajj = 1.0; if (i == 0) *bad = 1; }
-    const double d = sqrt(ajj), id = 1.0 / d;
+    const bool pos = ajj > 0.0;
+    bad |= !pos;
+    ajj = pos ? ajj : 1.0;
+    const double id = rsqrt(ajj), d = ajj * id;
     a[J] = (i == J) ? d : a[J] * id;
     if (i == J) idg[J] = id;
 #pragma unroll
@@ -394,22 +397,32 @@ __device__ __forceinline__ void chol_column(double (&a)[NX], int i, double *idg,
     if constexpr (J + 1 < NX) chol_column<J + 1>(a, i, idg, bad);
 }
 
-// Row-wise solve x L^T = a against LdT[t * 28 + c] = L[c][t] (right-looking), same reason for the recursion.
+// Row-wise solve x L^T = a against LdT[t * 28 + c] = L[c][t] (right-looking), same reason for the recursion.  LdT is
+// 16-byte aligned: aligned pairs of a row are fetched with one 128-bit broadcast load.
 template <int T>
 __device__ __forceinline__ void panel_column(double (&a)[NX], const double *LdT, const double *idg) {
     const double x = a[T] * idg[T];
     a[T] = x;
+    constexpr int C0 = (T + 1) + ((T + 1) & 1);              // first even column > T
+    if constexpr (((T + 1) & 1) && T + 1 < NX) a[T + 1] -= x * LdT[T * NX + T + 1];
 #pragma unroll
-    for (int c = T + 1; c < NX; ++c) a[c] -= x * LdT[T * NX + c];
+    for (int c = C0; c + 1 < NX; c += 2) {
+        const double2 v = *reinterpret_cast<const double2 *>(LdT + T * NX + c);
+        a[c] -= x * v.x;
+        a[c + 1] -= x * v.y;
+    }
     if constexpr (T + 1 < NX) panel_column<T + 1>(a, LdT, idg);
 }
 
+template <int R>
 __global__ void __launch_bounds__(256) band_block_kernel(const __grid_constant__ BandParams p) {
     extern __shared__ __align__(16) double smg[];
+    constexpr int WN = R * NX, nbk = R - 1, LD = WN + 1;
+    constexpr int NPRE = (NX * WN + 223) / 224;             // entries of one frame row per thread of warps 1-7
     const int tid = threadIdx.x, lane = tid & 31;
     const unsigned FULL = 0xffffffffu;
     const int s = blockIdx.x;
-    const int N = p.b.N, WN = p.bw + 1, R = WN / NX, nbk = R - 1, LD = WN + 1;
+    const int N = p.b.N;
     const int nf = p.b.n_frames[s];
     if (p.b.active && !p.b.active[s]) return;
     double *Wn = smg;                       // [WN][LD] ring window: frame f lives in slot f % R
@@ -418,6 +431,7 @@ __global__ void __launch_bounds__(256) band_block_kernel(const __grid_constant__
     double *idg = LdT + NX * NX;            // [32] 1 / diag(L_kk)
     double *bv = idg + 32;                  // [160] right-hand-side ring / backward solution ring
     double *zk = bv + 160;                  // [2][32]
+    double *Sst = zk + 64;                  // [2][28][LDP] frame-local blocks S_f, f & 1 (staged one frame ahead)
     __shared__ int bad;
     if (tid == 0) bad = 0;
     const double *Sg = p.S + (size_t)s * N * NX * NX;
@@ -425,51 +439,95 @@ __global__ void __launch_bounds__(256) band_block_kernel(const __grid_constant__
     const double *Mb = p.Mband + (size_t)s * p.mstride;
     double *Lb = p.Lband + (size_t)s * N * NX * WN;
     double *dl = p.delta + (size_t)s * N * NX;
-    // rows of frame f (lower part: column frames f - nbk .. f) into its ring slot
-    auto load_frame = [&](int f) {
-        const int sf = (f % R) * NX;
-        for (int e = tid; e < NX * WN; e += 256) {
-            const int r = e / WN, cc = e - r * WN;
-            const int g = f - nbk + cc / NX, c = cc % NX;
-            if (g < 0 || (g == f && c > r)) continue;
-            const int i = f * NX + r, col = g * NX + c;
-            double v = Mb[(size_t)i * WN + (i - col)];
-            if (g == f) v += Sg[(size_t)f * NX * NX + r * NX + c];
-            Wn[(sf + r) * LD + (g % R) * NX + c] = v;
-        }
-        if (tid < NX) bv[sf + tid] = -gh[(size_t)f * NX + tid];
+    // entry e of the rows of frame f (lower part of the constant band: column frames f - nbk .. f): offset of the value in
+    // Mband (0 where there is none, so that the load needs no branch), ring position, and whether it is stored
+    auto entry = [&](int f, int e, size_t &src, int &pos) -> bool {
+        const int r = e / WN, cc = e - r * WN;
+        const int g = f - nbk + cc / NX, c = cc % NX;
+        pos = ((f % R) * NX + r) * LD + ((g + R) % R) * NX + c;
+        const bool ok = g >= 0 && !(g == f && c > r);        // above the diagonal: never read
+        src = ok ? (size_t)(f * NX + r) * WN + ((f - g) * NX + r - c) : 0;
+        return ok;
     };
-    for (int f = 0; f < min(R, nf); ++f) load_frame(f);
+    for (int f = 0; f < min(R, nf); ++f) {
+        for (int e = tid; e < NX * WN; e += 256) {
+            size_t src; int pos;
+            if (entry(f, e, src, pos)) Wn[pos] = Mb[src];
+        }
+        if (tid < NX) bv[(f % R) * NX + tid] = -gh[(size_t)f * NX + tid];
+        if (f < 2)
+            for (int e = tid; e < NX * NX; e += 256) Sst[f * NX * LDP + (e / NX) * LDP + e % NX] = Sg[(size_t)f * NX * NX + e];
+    }
+    // tile of this thread in the trailing update (warps 1-7): lower tiles except the 10 of the next diagonal block
+    int ty = -1, tx = 0;
+    if (tid >= 32) {
+        int rem = tid - 32;
+        for (int y = 4; y < 4 * nbk; ++y) {
+            if (rem <= y) { ty = y; tx = rem; break; }
+            rem -= y + 1;
+        }
+    }
+    // diagonal block of frame f: minus the panel of frame f - 1 (if any), then Cholesky; warp 0 only
+    auto diag_factor = [&](int f, bool update) {
+        const int i = lane, ic = lane < NX ? lane : NX - 1;
+        const int sf = (f % R) * NX;
+        double a[NX];
+        {
+            // the part above the diagonal is stale shared memory: it is loaded but never feeds a lower entry
+            const double *row = Wn + (sf + ic) * LD + sf, *srow = Sst + (f & 1) * NX * LDP + ic * LDP;
+#pragma unroll
+            for (int c = 0; c < NX; ++c) a[c] = row[c] + srow[c];
+        }
+        if (update) {
+            double mine[NX];
+#pragma unroll
+            for (int t = 0; t < NX; ++t) mine[t] = Lp[ic * LDP + t];
+            // seven independent dot products at a time (a single one is a 28-long dependent FMA chain)
+#pragma unroll
+            for (int c0 = 0; c0 < NX; c0 += 7) {
+                double d[7];
+#pragma unroll
+                for (int j = 0; j < 7; ++j) d[j] = 0.0;
+#pragma unroll
+                for (int t = 0; t < NX; ++t)
+#pragma unroll
+                    for (int j = 0; j < 7; ++j) d[j] += mine[t] * Lp[(c0 + j) * LDP + t];
+#pragma unroll
+                for (int j = 0; j < 7; ++j) a[c0 + j] -= d[j];
+            }
+        }
+        int flag = 0;
+        chol_column<0>(a, i, idg, flag);
+        if (flag && lane == 0) bad = 1;
+        if (i < NX) {
+#pragma unroll
+            for (int t = 0; t < NX; ++t) LdT[t * NX + i] = a[t];          // entries with t > i are never read
+        }
+    };
+    __syncthreads();
+    if (tid < 32 && nf > 0) diag_factor(0, false);
     __syncthreads();
 
     for (int k = 0; k < nf; ++k) {
         const int m = min(nbk, nf - 1 - k);
         const int s0 = (k % R) * NX;
-        // ---- A: Cholesky of the diagonal block ----------------------------------------------------------------------
-        if (tid < 32) {
-            const int i = lane;
-            double a[NX];
-            {
-                // the part above the diagonal is stale shared memory: it is loaded but never feeds a lower entry
-                const double *row = Wn + (s0 + (i < NX ? i : NX - 1)) * LD + s0;
+        // rows of frame k + R: loads issued now, parked in the ring after the panel has been consumed
+        double pre[NPRE], preS[4];
+        const bool fetch = tid >= 32 && k + R < nf, fetchS = tid >= 32 && k + 2 < nf;
+        if (fetch) {
 #pragma unroll
-                for (int c = 0; c < NX; ++c) a[c] = row[c];
-            }
-            chol_column<0>(a, i, idg, &bad);
-            if (i < NX) {
-#pragma unroll
-                for (int t = 0; t < NX; ++t) LdT[t * NX + i] = a[t];      // entries with t > i are never read
+            for (int j = 0; j < NPRE; ++j) {
+                const int e = min(tid - 32 + 224 * j, NX * WN - 1);
+                size_t src; int pos;
+                entry(k + R, e, src, pos);
+                pre[j] = Mb[src];
             }
         }
-        __syncthreads();
-        // in-block part of the columns of L to HBM (threads that have no panel row)
-        if (tid >= 128) {
-            for (int e = tid - 128; e < NX * NX; e += 128) {
-                const int t = e / NX, i = e - t * NX;
-                if (i >= t) Lb[(size_t)(k * NX + t) * WN + (i - t)] = LdT[e];
-            }
+        if (fetchS) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) preS[j] = Sg[(size_t)(k + 2) * NX * NX + min(tid - 32 + 224 * j, NX * NX - 1)];
         }
-        // ---- B: panel rows (and the right-hand side as row 112) --------------------------------------------------------
+        // ---- B: panel rows (and the right-hand side as row 112); in-block columns of L to HBM ----------------------------
         if (tid < NX * m || tid == 112) {
             const bool rhs = tid == 112;
             const double *src = rhs ? bv + s0 : Wn + ((((k + 1 + tid / NX) % R) * NX + tid % NX) * LD + s0);
@@ -487,12 +545,19 @@ __global__ void __launch_bounds__(256) band_block_kernel(const __grid_constant__
                     Lb[(size_t)(k * NX + t) * WN + (NX - t + tid)] = a[t];
                 }
             }
+        } else if (tid >= 128) {
+            for (int e = tid - 128; e < NX * NX; e += 128) {
+                const int t = e / NX, i = e - t * NX;
+                if (i >= t) Lb[(size_t)(k * NX + t) * WN + (i - t)] = LdT[e];
+            }
         }
         __syncthreads();
-        // ---- C: trailing update (lower 7x7 tiles) + right-hand side ------------------------------------------------------
-        {
-            const int ty = tid >> 4, tx = tid & 15;
-            if (ty >= tx && 7 * ty < NX * m) {
+        if (tid < 32) {
+            // ---- A: next diagonal block ------------------------------------------------------------------------------
+            if (k + 1 < nf) diag_factor(k + 1, true);
+        } else {
+            // ---- C: trailing update (lower 7x7 tiles) + right-hand side ----------------------------------------------------
+            if (ty >= 0 && 7 * ty < NX * m) {
                 double acc[7][7];
 #pragma unroll
                 for (int i = 0; i < 7; ++i)
@@ -516,15 +581,31 @@ __global__ void __launch_bounds__(256) band_block_kernel(const __grid_constant__
 #pragma unroll
                     for (int j = 0; j < 7; ++j) Wn[(prow + i) * LD + pcol + j] -= acc[i][j];
             }
-            if (tid < NX * m) {
+            const int u = tid - 32;
+            if (u < NX * m) {
                 double acc = 0.0;
 #pragma unroll
-                for (int t = 0; t < NX; ++t) acc += Lp[tid * LDP + t] * zk[t];
-                bv[((k + 1 + tid / NX) % R) * NX + tid % NX] -= acc;
+                for (int t = 0; t < NX; ++t) acc += Lp[u * LDP + t] * zk[t];
+                bv[((k + 1 + u / NX) % R) * NX + u % NX] -= acc;
+            }
+            // ---- D: the freed slot takes frame k + R -----------------------------------------------------------------
+            if (fetch) {
+#pragma unroll
+                for (int j = 0; j < NPRE; ++j) {
+                    const int e = u + 224 * j;
+                    size_t src; int pos;
+                    if (e < NX * WN && entry(k + R, e, src, pos)) Wn[pos] = pre[j];
+                }
+                if (u < NX) bv[s0 + u] = -gh[(size_t)(k + R) * NX + u];
+            }
+            if (fetchS) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int e = u + 224 * j;
+                    if (e < NX * NX) Sst[(k & 1) * NX * LDP + (e / NX) * LDP + e % NX] = preS[j];
+                }
             }
         }
-        // ---- D: the freed slot takes frame k + R ---------------------------------------------------------------------
-        if (k + R < nf) load_frame(k + R);
         __syncthreads();
     }
     // ---- backward substitution L^T delta = z, one frame per step ---------------------------------------------------------
@@ -605,11 +686,20 @@ extern "C" int cpe_band_solve_general_f64(const cpe_batch *b, const double *Sblk
     const int WN = bw + 1;
     if (WN % cpe::NX == 0 && WN / cpe::NX >= 2 && WN / cpe::NX <= 5) {
         // whole frame blocks: blocked factorisation (3 barriers per frame)
-        const size_t smb = (size_t)(WN * (WN + 1) + 112 * cpe::LDP + cpe::NX * cpe::NX + 32 + 160 + 64) * sizeof(double);
-        cudaError_t eb = cudaFuncSetAttribute(cpe::band_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smb);
-        if (eb != cudaSuccess) return (int)eb;
-        cpe::band_block_kernel<<<b->S, 256, smb, (cudaStream_t)stream>>>(p);
-        return (int)cudaGetLastError();
+        const size_t smb = (size_t)(WN * (WN + 1) + 112 * cpe::LDP + cpe::NX * cpe::NX + 32 + 160 + 64 + 2 * cpe::NX * cpe::LDP) *
+                           sizeof(double);
+        auto launch = [&](auto kern) -> int {
+            cudaError_t eb = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smb);
+            if (eb != cudaSuccess) return (int)eb;
+            kern<<<b->S, 256, smb, (cudaStream_t)stream>>>(p);
+            return (int)cudaGetLastError();
+        };
+        switch (WN / cpe::NX) {
+            case 2: return launch(cpe::band_block_kernel<2>);
+            case 3: return launch(cpe::band_block_kernel<3>);
+            case 4: return launch(cpe::band_block_kernel<4>);
+            default: return launch(cpe::band_block_kernel<5>);
+        }
     }
     const size_t smem = (size_t)(WN * WN + 3 * WN) * sizeof(double);
     if (smem > 227 * 1024) return CPE_E_DIM;
