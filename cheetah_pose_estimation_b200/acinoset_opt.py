@@ -2,9 +2,10 @@
 413-536, 539-635): same function names, keyword arguments, output directories and file formats; the Pyomo model and
 the `ipopt` call are replaced by the CUDA path (engine.Solver).  `solver_path` is accepted and ignored.
 
-Not mirrored here (out of scope): kinetic mode (`determine_contacts`, `estimate_kinetics`,
-`estimate_grf`), shutter-delay estimation; the monocular data-driven priors (`monocular_constraints=True`) are the
-next row (section 8f.1) and raise NotImplementedError until their kernels exist.
+Mirrored beyond the multi-view reconstruction: the monocular data-driven priors (`monocular_constraints=True`,
+SURVEY.md section 8f.1), pairwise pseudo-measurements (`enable_ppm`), hand-labelled detections, and
+`CheetahEstimator.estimate_grf` (section 8f.3, first stage of the kinetic mode).  Not mirrored (out of scope,
+SURVEY.md section 8): `determine_contacts`, `estimate_kinetics` (full 54-row dynamics), shutter-delay estimation.
 """
 import json
 import os
@@ -78,6 +79,24 @@ class CheetahEstimator:
             return False
         ok = int(results["status"]) == 0 and np.isfinite(results["cost"]).all()
         return bool(ok and np.abs(results["c_eq"]).max() < 2e-3 and np.abs(results["v_in"]).max() < 2e-3)
+
+    def estimate_grf(self, plot: bool = False, monocular: bool = False, out_dir_prefix: Optional[str] = None,
+                     device: str = "cuda"):
+        """Reference: CheetahEstimator.estimate_grf (acinoset_opt.py:176-268).  Reads the kinematic trajectory saved by
+        `estimate_kinematics` (`fte_kinematic[_<cam>]/fte.pickle`) and `grf/autogen-contact.json`, solves every frame's
+        bounded least-squares problem on the GPU (kinetics.estimate_grf) and returns `(grfz_est, grfxy_est)`, dicts
+        keyed by foot name with one entry per frame.  `plot` is accepted and ignored (no matplotlib on this path)."""
+        import pickle
+        from . import kinetics
+        data_dir = self.params.data_dir if out_dir_prefix is None else os.path.join(
+            out_dir_prefix, self.params.data_dir.split("cheetah_videos")[1][1:])
+        sub = "fte_kinematic" if not monocular else f"fte_kinematic_{self.scene.cam_idx}"
+        with open(os.path.join(data_dir, sub, "fte.pickle"), "rb") as f:
+            fte_states = pickle.load(f)
+        with open(os.path.join(data_dir, "grf/autogen-contact.json"), "r", encoding="utf-8") as f:
+            metadata = json.load(f)
+        _ = plot
+        return kinetics.estimate_grf_states(fte_states, metadata, self.name, device=device)
 
     def joint_error(self, q: np.ndarray) -> Tuple[float, float]:
         return misc_rmse(q[:, :6], self.q[:, :6]), misc_rmse(q[:, 6:], self.q[:, 6:])

@@ -108,6 +108,30 @@ def test_estimate_grf_states_reference_return_shape(golden_dir):
 
 
 @pytest.mark.gpu
+def test_estimator_estimate_grf_reads_saved_trajectory(golden_dir, tmp_path):
+    """The mirror of CheetahEstimator.estimate_grf: files in the reference's places, same return value."""
+    import json
+    import pickle
+    from types import SimpleNamespace
+    from cheetah_pose_estimation_b200 import acinoset_opt, kinetics
+    g = np.load(os.path.join(golden_dir, "eom_ref.npz"))
+    n = 30
+    rep = lambda a: np.concatenate([a] * (n // a.shape[0] + 1))[:n]
+    st = {"q": rep(g["q"]), "dq": rep(g["dq"]), "ddq": rep(g["ddq"])}
+    os.makedirs(tmp_path / "fte_kinematic")
+    os.makedirs(tmp_path / "grf")
+    with open(tmp_path / "fte_kinematic" / "fte.pickle", "wb") as f:
+        pickle.dump(st, f)
+    with open(tmp_path / "grf" / "autogen-contact.json", "w", encoding="utf-8") as f:
+        json.dump(META, f)
+    est = acinoset_opt.CheetahEstimator("jules", "x", None, SimpleNamespace(data_dir=str(tmp_path)),
+                                        SimpleNamespace(cam_idx=None), 1.0, None, True, True)
+    gz, gxy = est.estimate_grf()
+    gz2, gxy2 = kinetics.estimate_grf_states(st, META, "jules")
+    assert gz == gz2 and gxy == gxy2 and len(gz["HFL_foot"]) == n
+
+
+@pytest.mark.gpu
 def test_grf_estimate_matches_oracle_value(golden_dir):
     """Optimal VALUE parity (the minimiser is not unique): | r_gpu - r_oracle | <= 1e-9 ||a|| and never below the oracle's
     by more than that; the GPU forces are feasible to 1e-12 and reproduce their own residual through cpe_eom_f64."""
