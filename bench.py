@@ -46,7 +46,7 @@ def parse_args():
     ap.add_argument("--frames", type=int, default=500)
     ap.add_argument("--cams", type=int, default=6)
     ap.add_argument("--wave", type=int, default=512, help="sequences per launch (Jacobian buffer reuse)")
-    ap.add_argument("--lm-seqs", type=int, default=444, help="sequences of the LM-solve leg (0 = skip)")
+    ap.add_argument("--lm-seqs", type=int, default=1776, help="sequences of the LM-solve leg (0 = skip)")
     ap.add_argument("--lm-iters", type=int, default=20)
     ap.add_argument("--lm-split", type=int, default=1, help="sub-batches of the LM leg solved on separate streams")
     ap.add_argument("--mono-seqs", type=int, default=60, help="monocular hypotheses of the config-3 leg (0 = skip)")
