@@ -422,7 +422,7 @@ def grf_leg(a, r):
     e1.record()
     r["barrier"]()
     ms = e0.elapsed_time(e1)
-    return {"sequences": S, "frames": S * N, "frames_per_s": S * N / (ms * 1e-3), "ms": ms, "iterations": 600,
+    return {"sequences": S, "frames": S * N, "frames_per_s": S * N / (ms * 1e-3), "ms": ms, "max_iterations": 600,
             "launches": 2, "resid_mean": float(resid.mean()), "grf_max": float(grf.max())}
 
 

@@ -281,7 +281,8 @@ int cpe_eom_affine_f64(const cpe_batch *batch, const double *q, const double *dq
 /* Per-frame GRF estimate of CheetahEstimator.estimate_grf (acinoset_opt.py:176-249): minimise || a - Bm F || over
  * 0 <= F <= 5 with the friction polyhedron 1.3 GRFz[f] >= sum_i GRFxy[f][i] (:187-190); contact[S,N,4] != 0 marks the
  * feet on the ground, the forces of the others are fixed to 0 (:221-229).  Accelerated projected gradient with adaptive
- * restart, `iters` iterations (600 reaches the optimum value to ~1e-14 ||a|| on the fixture).  grf[S,N,20], resid[S,N] = the optimal || eom ||. */
+ * restart, at most `iters` iterations (a frame stops once its iterate is a fixed point to 1e-13; 600 reaches the
+ * optimum value to ~1e-14 ||a|| on the fixture).  grf[S,N,20], resid[S,N] = the optimal || eom ||. */
 int cpe_grf_solve_f64(const cpe_batch *batch, const double *a, const double *Bm, const int32_t *contact, int32_t iters,
                       double *grf, double *resid, void *stream);
 
