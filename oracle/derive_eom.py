@@ -167,7 +167,33 @@ def golden(rows, inputs, values, path, n=24, seed=11):
     print("golden eom rows, first frame:", out[0])
 
 
+def golden_clip(rows, inputs, values, path, clip=0):
+    """a, Bm of the same expressions on a REAL shipped trajectory: q, dq, ddq of clip `clip` of
+    tests/golden/shipped_clips.npz (2017_08_29/top/jules/run1_1/fte_kinematic, 30 frames from frame 53), the input of
+    the reference's estimate_grf for that clip together with its grf/autogen-contact.json."""
+    import sympy as sp
+    func_map = {"sqrt": lambda x: (x + 1e-9) ** (1 / 2)}
+    fn = sp.lambdify(inputs, rows, modules=[func_map, "math"], cse=True)
+    g = np.load(os.path.join(ROOT, "tests", "golden", "shipped_clips.npz"))
+    assert str(g["names"][clip]).endswith("run1_1/fte_kinematic|jules")
+    q, dq, ddq = g[f"{clip}_q"], g[f"{clip}_dq"], g[f"{clip}_ddq"]
+    n = q.shape[0]
+    par = np.concatenate([values["lengths"], values["masses"], values["radii"], [sum(values["masses"]) * 9.81]])
+    z = np.zeros(20)
+    a = np.array([fn(*np.concatenate([q[i], dq[i], ddq[i], z, par])) for i in range(n)], dtype=float)
+    Bm = np.zeros((n, 6, 20))
+    for j in range(20):
+        e = np.zeros(20)
+        e[j] = 1.0
+        Bm[:, :, j] = a - np.array([fn(*np.concatenate([q[i], dq[i], ddq[i], e, par])) for i in range(n)], dtype=float)
+    np.savez_compressed(path, q=q, dq=dq, ddq=ddq, par=par, a=a, Bm=Bm)
+    print("golden clip rows at F = 0, first frame:", a[0])
+
+
 if __name__ == "__main__":
+    import sys
     rows, inputs, values = derive()
-    emit_cuda(rows, inputs, os.path.join(ROOT, "cheetah_pose_estimation_b200", "csrc", "cpe_eom_gen.cuh"))
-    golden(rows, inputs, values, os.path.join(ROOT, "tests", "golden", "eom_ref.npz"))
+    if "--clip-only" not in sys.argv:
+        emit_cuda(rows, inputs, os.path.join(ROOT, "cheetah_pose_estimation_b200", "csrc", "cpe_eom_gen.cuh"))
+        golden(rows, inputs, values, os.path.join(ROOT, "tests", "golden", "eom_ref.npz"))
+    golden_clip(rows, inputs, values, os.path.join(ROOT, "tests", "golden", "eom_clip_ref.npz"))

@@ -154,3 +154,37 @@ def test_grf_estimate_matches_oracle_value(golden_dir):
     rows = kinetics.eom_rows(g["q"][:n, None], g["dq"][:n, None], g["ddq"][:n, None], F[:, None], g["par"][:n])
     rr = np.linalg.norm(rows[:, 0].cpu().numpy(), axis=1)
     assert np.abs(rr - r).max() <= 1e-9 * np.abs(g["a"][:n]).max()
+
+
+# grf/autogen-contact.json of data/test_set/2017_08_29/top/jules/run1_1 (what the reference's estimate_grf reads next to
+# fte_kinematic/fte.pickle); the trajectory itself is clip 0 of tests/golden/shipped_clips.npz
+CLIP_META = {"start_frame": 53, "end_frame": 83,
+             "contacts": {"HFL_foot": [[58, 64, 0, "leading"]], "HFR_foot": [[54, 60, 1, "trailing"]],
+                          "HBL_foot": [[69, 75, 2, "trailing"]], "HBR_foot": [[72, 78, 3, "leading"]]}}
+
+
+@pytest.mark.gpu
+def test_grf_of_a_real_shipped_trajectory(golden_dir):
+    """estimate_grf on the reference's own kinematic solution of jules/run1_1 (30 frames) with its shipped contact
+    ranges: a and Bm against the reference expressions (1e-9), optimal value per frame against the SLSQP oracle."""
+    from cheetah_pose_estimation_b200 import kinetics
+    from oracle import grf as ogrf
+    g = np.load(os.path.join(golden_dir, "eom_clip_ref.npz"))
+    n = g["q"].shape[0]
+    assert np.allclose(g["par"], kinetics.link_params("jules"), rtol=0, atol=1e-15)
+    ct = kinetics.contact_mask(CLIP_META)
+    assert ct.shape == (n, 4) and ct.sum(axis=0).tolist() == [6, 6, 6, 6]
+    st = {k: g[k] for k in ("q", "dq", "ddq")}
+    gz, gxy = kinetics.estimate_grf_states(st, CLIP_META, "jules")
+    zero = np.zeros((1, n, 20))
+    rows0 = kinetics.eom_rows(g["q"][None], g["dq"][None], g["ddq"][None], zero, g["par"][None])[0].cpu().numpy()
+    assert np.abs(rows0 - g["a"]).max() <= 1e-9 * np.abs(g["a"]).max()
+    for fe in range(n):
+        F = np.array([gz[f][fe] for f in kinetics.FEET] + [v for f in kinetics.FEET for v in gxy[f][fe]])
+        r_gpu = np.linalg.norm(g["a"][fe] - g["Bm"][fe] @ F)
+        _, r_ref = ogrf.solve_frame(g["a"][fe], g["Bm"][fe], ct[fe])
+        assert abs(r_gpu - r_ref) <= 1e-8 * np.linalg.norm(g["a"][fe]), (fe, r_gpu, r_ref)
+        if not ct[fe].any():
+            assert not F.any()
+    # stance forces point up: vertical force of every foot in contact is positive somewhere in its stance
+    assert all(max(gz[f]) > 0.0 for f in kinetics.FEET)
