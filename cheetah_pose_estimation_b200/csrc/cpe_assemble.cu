@@ -363,6 +363,10 @@ static int launch_asm(const AsmParams &p, dim3 grid, int threads, size_t smem, c
     cudaError_t e = cudaFuncSetAttribute(assemble_kernel<MAXT, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)smem);
     if (e != cudaSuccess) return (int)e;
+    // all of the L1/shared array as shared memory: the default carve-out stops at 5 CTAs of 31 KB
+    e = cudaFuncSetAttribute(assemble_kernel<MAXT, MINB>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                             cudaSharedmemCarveoutMaxShared);
+    if (e != cudaSuccess) return (int)e;
     assemble_kernel<MAXT, MINB><<<grid, threads, smem, st>>>(p);
     return (int)cudaGetLastError();
 }
@@ -391,6 +395,6 @@ extern "C" int cpe_assemble_f64(const cpe_model *model, const cpe_batch *b, cons
     int threads = ((p.TPF + 31) / 32) * 32;
     if (threads < 160) threads = 160;               // >= 5 warps: one per elimination group
     const dim3 grid(b->N, b->S, 1);
-    if (threads <= 160) return launch_asm<160, 5>(p, grid, threads, smem, (cudaStream_t)stream);
+    if (threads <= 160) return launch_asm<160, 6>(p, grid, threads, smem, (cudaStream_t)stream);
     return launch_asm<192, 4>(p, grid, threads, smem, (cudaStream_t)stream);
 }
