@@ -379,22 +379,33 @@ constexpr int LDP = 29;
 
 // Column J of the in-register Cholesky (lane i holds row i).  A template recursion instead of `#pragma unroll`: nvcc
 // leaves the triangular double loop partly rolled, which puts the row into local memory.
+// The finished column goes straight to its place in LdT (LdT[J * 28 + i] = L[i][J]) and is read back by every lane
+// with 128-bit broadcast loads: 14 loads per column instead of 54 shuffles.
 template <int J>
-__device__ __forceinline__ void chol_column(double (&a)[NX], int i, double *idg, int &bad) {
+__device__ __forceinline__ void chol_column(double (&a)[NX], int i, double *LdT, double *idg, int &bad) {
     const unsigned FULL = 0xffffffffu;
     double ajj = __shfl_sync(FULL, a[J], J);
     const bool pos = ajj > 0.0;
     bad |= !pos;
     ajj = pos ? ajj : 1.0;
     const double id = rsqrt(ajj), d = ajj * id;
-    a[J] = (i == J) ? d : a[J] * id;
+    const double l = (i == J) ? d : a[J] * id;               // lanes i < J carry stale values that are never read
+    a[J] = l;
     if (i == J) idg[J] = id;
-#pragma unroll
-    for (int c = J + 1; c < NX; ++c) {
-        const double lc = __shfl_sync(FULL, a[J], c);
-        if (i >= c) a[c] -= a[J] * lc;
+    if (i < NX) LdT[J * NX + i] = l;
+    __syncwarp();
+    constexpr int C0 = (J + 1) + ((J + 1) & 1);              // first even row > J
+    if constexpr (((J + 1) & 1) && J + 1 < NX) {
+        const double lc = LdT[J * NX + J + 1];
+        if (i >= J + 1) a[J + 1] -= l * lc;
     }
-    if constexpr (J + 1 < NX) chol_column<J + 1>(a, i, idg, bad);
+#pragma unroll
+    for (int c = C0; c + 1 < NX; c += 2) {
+        const double2 v = *reinterpret_cast<const double2 *>(LdT + J * NX + c);
+        if (i >= c) a[c] -= l * v.x;
+        if (i >= c + 1) a[c + 1] -= l * v.y;
+    }
+    if constexpr (J + 1 < NX) chol_column<J + 1>(a, i, LdT, idg, bad);
 }
 
 // Row-wise solve x L^T = a against LdT[t * 28 + c] = L[c][t] (right-looking), same reason for the recursion.  LdT is
@@ -467,8 +478,8 @@ __global__ void __launch_bounds__(256) band_block_kernel(const __grid_constant__
             rem -= y + 1;
         }
     }
-    // diagonal block of frame f: minus the panel of frame f - 1 (if any), then Cholesky; warp 0 only
-    auto diag_factor = [&](int f, bool update) {
+    // Cholesky of the diagonal block of frame f (the panel of frame f - 1 has been applied by warps 5-7); warp 0 only
+    auto diag_factor = [&](int f) {
         const int i = lane, ic = lane < NX ? lane : NX - 1;
         const int sf = (f % R) * NX;
         double a[NX];
@@ -478,34 +489,12 @@ __global__ void __launch_bounds__(256) band_block_kernel(const __grid_constant__
 #pragma unroll
             for (int c = 0; c < NX; ++c) a[c] = row[c] + srow[c];
         }
-        if (update) {
-            double mine[NX];
-#pragma unroll
-            for (int t = 0; t < NX; ++t) mine[t] = Lp[ic * LDP + t];
-            // seven independent dot products at a time (a single one is a 28-long dependent FMA chain)
-#pragma unroll
-            for (int c0 = 0; c0 < NX; c0 += 7) {
-                double d[7];
-#pragma unroll
-                for (int j = 0; j < 7; ++j) d[j] = 0.0;
-#pragma unroll
-                for (int t = 0; t < NX; ++t)
-#pragma unroll
-                    for (int j = 0; j < 7; ++j) d[j] += mine[t] * Lp[(c0 + j) * LDP + t];
-#pragma unroll
-                for (int j = 0; j < 7; ++j) a[c0 + j] -= d[j];
-            }
-        }
         int flag = 0;
-        chol_column<0>(a, i, idg, flag);
+        chol_column<0>(a, i, LdT, idg, flag);                  // leaves L_kk in LdT (entries with t > i are never read)
         if (flag && lane == 0) bad = 1;
-        if (i < NX) {
-#pragma unroll
-            for (int t = 0; t < NX; ++t) LdT[t * NX + i] = a[t];          // entries with t > i are never read
-        }
     };
     __syncthreads();
-    if (tid < 32 && nf > 0) diag_factor(0, false);
+    if (tid < 32 && nf > 0) diag_factor(0);
     __syncthreads();
 
     for (int k = 0; k < nf; ++k) {
@@ -554,8 +543,38 @@ __global__ void __launch_bounds__(256) band_block_kernel(const __grid_constant__
         __syncthreads();
         if (tid < 32) {
             // ---- A: next diagonal block ------------------------------------------------------------------------------
-            if (k + 1 < nf) diag_factor(k + 1, true);
+            if (k + 1 < nf) {
+                asm volatile("bar.sync 1, 128;" ::: "memory");     // the 70 strips of warps 5-7 are in place
+                diag_factor(k + 1);
+            }
         } else {
+            if (tid >= 160 && k + 1 < nf) {
+                // warps 5-7 own no trailing tile: they apply the panel to the NEXT diagonal block first, as 1x7 strips
+                // of its ten lower 7x7 tiles, and hand it to warp 0 through named barrier 1
+                const int v = tid - 160;
+                if (v < 70) {
+                    const int tl = v / 7, ri = v - 7 * tl;
+                    const int ty2 = tl < 1 ? 0 : (tl < 3 ? 1 : (tl < 6 ? 2 : 3));
+                    const int tx2 = tl - (ty2 * (ty2 + 1)) / 2;
+                    const int r = 7 * ty2 + ri, c0 = 7 * tx2;
+                    double d[7];
+#pragma unroll
+                    for (int j = 0; j < 7; ++j) d[j] = 0.0;
+#pragma unroll 4
+                    for (int t = 0; t < NX; ++t) {
+                        const double x = Lp[r * LDP + t];
+#pragma unroll
+                        for (int j = 0; j < 7; ++j) d[j] += x * Lp[(c0 + j) * LDP + t];
+                    }
+                    const int s1 = ((k + 1) % R) * NX;
+                    double *w = Wn + (s1 + r) * LD + s1 + c0;
+#pragma unroll
+                    for (int j = 0; j < 7; ++j) w[j] -= d[j];
+                }
+                __threadfence_block();
+                __syncwarp();                                      // bar.* is warp-aligned: reconverge first
+                asm volatile("bar.arrive 1, 128;" ::: "memory");
+            }
             // ---- C: trailing update (lower 7x7 tiles) + right-hand side ----------------------------------------------------
             if (ty >= 0 && 7 * ty < NX * m) {
                 double acc[7][7];
