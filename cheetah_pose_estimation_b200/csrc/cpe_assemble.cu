@@ -385,6 +385,7 @@ extern "C" int cpe_assemble_f64(const cpe_model *model, const cpe_batch *b, cons
         !model->s_items || !model->ent_order || !model->s_order)
         return CPE_E_NULL;
     if (out->S && (!damp || !out->ghat || !out->Y || !out->y)) return CPE_E_NULL;
+    if (b->shutter_tau || b->base_dq || b->base_ddq) return CPE_E_ARG;   // delay estimation is not on the LM path (cpe.h)
     AsmParams p;
     p.m = *model; p.b = *b; p.q = q; p.damp = damp; p.ao = *out;
     p.TPF = b->C * 24;

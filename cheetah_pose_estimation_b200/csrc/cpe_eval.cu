@@ -188,8 +188,16 @@ __global__ void __launch_bounds__(WPC * 32, MINB) eval_kernel(const __grid_const
             // base origin in the camera frame: tc = R_c base + t_c (FP64)
             const int c = lane / 3, r = lane - 3 * c;
             const double *cm = camd + c * CPE_CAM_STRIDE;
-            tcv[lane] = (T)(cm[8 + 3 * r] * wd[QO + 0] + cm[9 + 3 * r] * wd[QO + 1] + cm[10 + 3 * r] * wd[QO + 2] +
-                            cm[17 + r]);
+            double bx = wd[QO + 0], by = wd[QO + 1], bz = wd[QO + 2];
+            if (p.b.shutter_tau) {
+                // shutter delay: camera c sees the frame displaced by dq tau_c + ddq tau_c^2 (acinoset_misc.py:280-286)
+                const double tau = p.b.shutter_tau[(size_t)s * C + c];
+                const double *vb = p.b.base_dq + (size_t)fi * 3, *ab = p.b.base_ddq + (size_t)fi * 3;
+                bx = bx + vb[0] * tau + ab[0] * (tau * tau);
+                by = by + vb[1] * tau + ab[1] * (tau * tau);
+                bz = bz + vb[2] * tau + ab[2] * (tau * tau);
+            }
+            tcv[lane] = (T)(cm[8 + 3 * r] * bx + cm[9 + 3 * r] * by + cm[10 + 3 * r] * bz + cm[17 + r]);
         }
         if (lane < 26) {
             const int e = lane;
@@ -343,6 +351,7 @@ static int launch_eval(const cpe_model *model, const cpe_batch *b, const double 
     if (b->meas_layout < 0 || b->meas_layout > CPE_MEAS_F32X3) return CPE_E_ARG;
     if (!b->meas || !b->cams || !b->chain_vec || !b->n_frames || !b->h) return CPE_E_NULL;
     if (!model->u_off || !model->u_item) return CPE_E_NULL;
+    if ((b->shutter_tau || b->base_dq || b->base_ddq) && !(b->shutter_tau && b->base_dq && b->base_ddq)) return CPE_E_NULL;
     constexpr bool f64 = sizeof(T) == 8;
     constexpr int WPC = 4;
     const bool jac = eo->jac != nullptr;

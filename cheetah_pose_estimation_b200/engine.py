@@ -74,6 +74,10 @@ class Batch:
     dlc_thresh: float = 0.5
     loss_mode: int = LOSS_REDESCENDING
     active: torch.Tensor = None  # [S] int32, optional: sequences with 0 are skipped by every kernel
+    # shutter delay of the measurement model (acinoset_misc.py:273-286); evaluation only, see include/cpe.h
+    shutter_tau: torch.Tensor = None   # [S,C] f64 seconds
+    base_dq: torch.Tensor = None       # [S,N,3] f64
+    base_ddq: torch.Tensor = None      # [S,N,3] f64
 
     @property
     def meas_layout(self):
@@ -118,6 +122,13 @@ class Batch:
         b.lam_eq = self.lam_eq.data_ptr() if self.lam_eq is not None else None
         b.lam_in = self.lam_in.data_ptr() if self.lam_in is not None else None
         b.active = self.active.data_ptr() if self.active is not None else None
+        if self.shutter_tau is not None:
+            for t, shp in ((self.shutter_tau, (self.S, self.C)), (self.base_dq, (self.S, self.N, 3)),
+                           (self.base_ddq, (self.S, self.N, 3))):
+                assert t is not None and t.is_cuda and t.is_contiguous() and t.dtype == torch.float64
+                assert tuple(t.shape) == shp
+            b.shutter_tau, b.base_dq, b.base_ddq = (self.shutter_tau.data_ptr(), self.base_dq.data_ptr(),
+                                                    self.base_ddq.data_ptr())
         return b
 
     def window(self, s0, s1):
@@ -128,7 +139,10 @@ class Batch:
                      lam_in=None if self.lam_in is None else self.lam_in[s0:s1],
                      mu_eq=self.mu_eq, mu_in=self.mu_in, loss=self.loss, dlc_thresh=self.dlc_thresh,
                      loss_mode=self.loss_mode,
-                     active=None if self.active is None else self.active[s0:s1])
+                     active=None if self.active is None else self.active[s0:s1],
+                     shutter_tau=None if self.shutter_tau is None else self.shutter_tau[s0:s1],
+                     base_dq=None if self.base_dq is None else self.base_dq[s0:s1],
+                     base_ddq=None if self.base_ddq is None else self.base_ddq[s0:s1])
 
     @staticmethod
     def from_numpy(meas, cams, chain_vec, h, n_frames=None, device="cuda", cam_model=FISHEYE, meas_dtype=torch.float32,
@@ -417,6 +431,21 @@ class Solver:
         if self.priors is not None:
             res["prior_cost"] = out["prior_cost"].clone()
         self.result = res
+
+
+def shutter_jacobian(jac, batch):
+    """d slack / d tau_c, [S,N,C,24,2], from the packed Jacobian of `Solver.evaluate(jac=True)` on a batch with a
+    shutter delay: the base x, y, z columns of a marker ARE d(u,v)/d(point), so
+    d slack / d tau_c = d(u,v)/d(point) . (dq_base + 2 tau_c ddq_base)   (derivative of acinoset_misc.py:283-286).
+    Likewise d slack / d dq_base = tau_c d(u,v)/d(point) and d slack / d ddq_base = tau_c^2 d(u,v)/d(point).
+    Device-side torch indexing of the kernel's output; no kernel of its own."""
+    u_off, _, _ = skeleton.jacobian_pattern()
+    start = torch.as_tensor([2 * (3 * l + int(u_off[l])) for l in range(24)], device=jac.device)
+    idx = start[:, None] + torch.arange(6, device=jac.device)[None, :]                     # [24,6]
+    P = jac[..., idx].reshape(*jac.shape[:-1], 24, 3, 2).to(torch.float64)                 # [S,N,C,24,xyz,uv]
+    tau = batch.shutter_tau[:, None, :, None]                                              # [S,1,C,1]
+    d = batch.base_dq[:, :, None, :] + 2.0 * tau * batch.base_ddq[:, :, None, :]           # [S,N,C,3]
+    return torch.einsum("snclid,snci->sncld", P, d)
 
 
 def solve_split(model, batch, q0, n_split=2, priors=None, **kw):

@@ -128,6 +128,15 @@ typedef struct cpe_batch {
     const double *lam_in;           /* [S,N,n_ineq] (may be NULL = 0) */
     const int32_t *active;          /* [S] optional (NULL = all): sequences with active == 0 are skipped by every kernel
                                        (their outputs keep their previous contents) -- converged sequences of an LM loop */
+    /* Shutter delay of the measurement model (acinoset_misc.py:182-183, 273-286; acinoset_opt.py:342-352): camera c sees
+       every marker of frame n displaced by  dq_base[n] tau_c + ddq_base[n] tau_c^2  (no 1/2, as in the reference).
+       All three NULL = no delay.  cpe_eval_* honours them (residuals, costs, Jacobian d slack / d q_n at fixed dq, ddq,
+       tau -- the reference's own partial derivative, dq and ddq being separate NLP variables there; eo.pose stays the
+       undelayed FK, the reference's `positions`).  cpe_assemble_f64 (the LM normal equations) returns
+       CPE_E_ARG when a delay is set: estimating tau is not on this path yet. */
+    const double *shutter_tau;      /* [S,C] seconds; the reference fixes camera 1 at 0 and bounds the rest by +-1/fps */
+    const double *base_dq;          /* [S,N,3] velocity of base x, y, z     (robot["base"]["dq"][n, 1, .]) */
+    const double *base_ddq;         /* [S,N,3] acceleration of base x, y, z (robot["base"]["ddq"][n, 1, .]) */
 } cpe_batch;
 
 /* Optional outputs of cpe_eval (NULL = skip). */

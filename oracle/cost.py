@@ -84,15 +84,39 @@ class Problem:
         return self.meas.shape[0]
 
 
-def residuals(pb: Problem, q):
-    """slack[N,C,L,W,2] = proj(pose) - meas  (what the reference saves as `meas_err`)."""
+def delayed_pose(pb: Problem, q, tau=None, dq_base=None, ddq_base=None):
+    """Marker positions as camera c sees them, [N,C,24,3]:  pose + dq_base tau_c + ddq_base tau_c^2
+    (acinoset_misc.py:280-286; the same expression in acinoset_opt.py:342-352 for the saved 2-D outputs).
+    tau[C] seconds (the reference fixes tau[0] = 0, :274-275), dq_base / ddq_base [N,3] = the base x, y, z entries of
+    the reference's dq / ddq variables.  tau None = no delay."""
     pose = kinematics.fk(q, pb.chain_link, pb.chain_vec)                     # [N,24,3]
-    uv = cameras.project(pose[:, None, :, :], pb.cams[None, :, None, :], pb.cam_model)   # [N,C,L,2]
+    C = pb.cams.shape[0]
+    if tau is None:
+        return np.broadcast_to(pose[:, None], (pose.shape[0], C, 24, 3))
+    tau = np.asarray(tau, float)
+    off = (np.asarray(dq_base, float)[:, None, :] * tau[None, :, None]
+           + np.asarray(ddq_base, float)[:, None, :] * (tau ** 2)[None, :, None])          # [N,C,3]
+    return pose[:, None, :, :] + off[:, :, None, :]
+
+
+def residuals(pb: Problem, q, tau=None, dq_base=None, ddq_base=None):
+    """slack[N,C,L,W,2] = proj(pose [+ shutter-delay displacement]) - meas  (what the reference saves as `meas_err`)."""
+    pts = delayed_pose(pb, q, tau, dq_base, ddq_base)                        # [N,C,24,3]
+    uv = cameras.project(pts, pb.cams[None, :, None, :], pb.cam_model)       # [N,C,L,2]
     return uv[:, :, :, None, :] - pb.meas[..., 0:2]
 
 
-def measurement_cost(pb: Problem, q):
-    r = residuals(pb, q)
+def shutter_jacobian(pb: Problem, q, tau, dq_base, ddq_base):
+    """d slack / d tau_c, [N,C,L,2] = dproj/dpoint . (dq_base + 2 tau_c ddq_base)  (derivative of :283-286)."""
+    pts = delayed_pose(pb, q, tau, dq_base, ddq_base)
+    P = cameras.project_jacobian(pts, pb.cams[None, :, None, :], pb.cam_model)             # [N,C,L,2,3]
+    tau = np.asarray(tau, float)
+    d = np.asarray(dq_base, float)[:, None, :] + 2.0 * tau[None, :, None] * np.asarray(ddq_base, float)[:, None, :]
+    return np.einsum("ncldi,nci->ncld", P, d)
+
+
+def measurement_cost(pb: Problem, q, tau=None, dq_base=None, ddq_base=None):
+    r = residuals(pb, q, tau, dq_base, ddq_base)
     e = pb.meas[..., 2:3] * r
     if pb.square_loss:
         return float(np.sum(e * e))

@@ -381,3 +381,72 @@ def test_square_loss_mode_matches_oracle(gpu):
         g = g + cost.motion_gradient(pb, q[s])
         assert _rel(Hraw[s].cpu().numpy(), H) < RTOL
         assert _rel(sv.g[s].cpu().numpy(), g) < RTOL
+
+
+def test_shutter_delay_evaluation(gpu, golden_dir):
+    """Shutter-delay term of the measurement model (acinoset_misc.py:273-288): K1's residuals, cost and Jacobian with
+    per-camera delays against the oracle and against the reference-function golden; d slack / d tau from the packed
+    Jacobian; the LM normal equations refuse a delayed batch (estimating tau is not on this path)."""
+    import ctypes as C
+    import torch
+    from cheetah_pose_estimation_b200 import _lib, engine, skeleton
+    from oracle import cameras, cost, kinematics
+    g = np.load(os.path.join(golden_dir, "shutter_ref.npz"))
+    clip = np.load(os.path.join(golden_dir, "clip_jules_run1_1.npz"))
+    N, Cn = clip["detections"].shape[:2]
+    lengths, radii, _ = skeleton.animal("jules")
+    cl, cvec = skeleton.marker_chains(lengths, radii)
+    meas = np.zeros((2, N, Cn, 24, 1, 4), np.float32)
+    meas[:, :, :, :, 0, 0:2] = clip["detections"]
+    meas[..., 2] = 1.0
+    cams = np.zeros((2, Cn, 24))
+    cams[:, :, :20] = clip["cams"]
+    cams[:, :, 20] = 1.0
+    h = 1.0 / float(clip["fps"])
+    batch = engine.Batch.from_numpy(meas, cams, np.stack([cvec, cvec]), [h, h])
+    tau = np.stack([g["tau"], -0.5 * g["tau"]])                     # second sequence: different delays, same clip
+    dev = dict(device="cuda:0", dtype=torch.float64)
+    batch.shutter_tau = torch.as_tensor(tau, **dev).contiguous()
+    batch.base_dq = torch.as_tensor(np.stack([clip["dq"][:, 0:3]] * 2), **dev).contiguous()
+    batch.base_ddq = torch.as_tensor(np.stack([clip["ddq"][:, 0:3]] * 2), **dev).contiguous()
+    solver = engine.Solver(gpu, batch, with_solver=False)
+    qd = torch.as_tensor(np.stack([clip["q"]] * 2), **dev).contiguous()
+    out = solver.evaluate(qd, pose=True, resid=True, jac=True)
+    torch.cuda.synchronize()
+    got = out["resid"][:, :, :, :, 0, :].cpu().numpy()
+    # golden from the reference's own functions (10 frames of sequence 0)
+    ref = g["slack"]
+    assert (np.abs(got[0][g["frames"]] - ref) / np.maximum(np.abs(ref), 1.0)).max() < RTOL
+    # the saved positions stay the undelayed FK (acinoset_opt.py:354: positions_arr[0], camera 1 has tau = 0)
+    assert np.abs(out["pose"][0].cpu().numpy() - clip["positions"]).max() < 1e-13
+    om = np.concatenate([clip["detections"].astype(float), np.ones((N, Cn, 24, 1))], -1)[:, :, :, None, :]
+    pb = cost.Problem(meas=om, cams=clip["cams"], chain_link=cl, chain_vec=cvec, h=h)
+    dense = skeleton.jacobian_to_dense(out["jac"].cpu().numpy())
+    Jt = engine.shutter_jacobian(out["jac"], batch).cpu().numpy()
+    for s in range(2):
+        args = (tau[s], clip["dq"][:, 0:3], clip["ddq"][:, 0:3])
+        r = cost.residuals(pb, clip["q"], *args)[:, :, :, 0, :]
+        assert (np.abs(got[s] - r) / np.maximum(np.abs(r), 1.0)).max() < RTOL
+        mc = cost.measurement_cost(pb, clip["q"], *args)
+        assert abs(float(out["cost"][s, 0]) - mc) <= RTOL * mc
+        pts = cost.delayed_pose(pb, clip["q"], *args)                                   # [N,C,24,3]
+        G = kinematics.fk_jacobian(clip["q"], cl, cvec)                                 # [N,24,3,54]
+        P = cameras.project_jacobian(pts, pb.cams[None, :, None, :])                    # [N,C,24,2,3]
+        J = np.einsum("ncldi,nlia->nclda", P, G)
+        scale = np.abs(J).max(axis=-1, keepdims=True)
+        assert (np.abs(dense[s] - J) / np.maximum(scale, 1.0)).max() < RTOL
+        Jo = cost.shutter_jacobian(pb, clip["q"], *args)
+        assert np.abs(Jt[s] - Jo).max() <= RTOL * np.abs(Jo).max()
+    # FP32 flavour honours the delay as well
+    out32 = solver.evaluate(qd, resid=True, f32=True)
+    torch.cuda.synchronize()
+    r32 = out32["resid"][:, :, :, :, 0, :].cpu().numpy()
+    assert (np.abs(r32 - got) / np.maximum(np.abs(got), 1.0)).max() < 1e-4
+    # the LM assembly refuses a delayed batch loudly
+    ao = _lib.CpeAssembleOut()
+    gbuf = torch.zeros(2, N, 54, **dev)
+    dbuf = torch.zeros(2, N, 54, **dev)
+    ao.g, ao.diagH = gbuf.data_ptr(), dbuf.data_ptr()
+    bs = batch.struct()
+    rc = gpu.lib.cpe_assemble_f64(C.byref(gpu.struct), C.byref(bs), C.c_void_p(qd.data_ptr()), None, C.byref(ao), None)
+    assert rc == -1

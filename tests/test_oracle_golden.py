@@ -185,3 +185,29 @@ def test_gradient_and_gn_blocks_are_consistent(golden_dir):
     A, gvec = cost.dense_hessian(pb, q, lam_eq, lam_in)
     assert np.allclose(A, A.T)
     assert np.linalg.eigvalsh(A).min() > -1e-6 * np.abs(A).max()
+
+
+def test_shutter_delay_residuals_match_reference_expression(golden_dir):
+    """slack = proj(pose + dq_base tau_c + ddq_base tau_c^2) - meas, evaluated by the reference's own lambdified FK
+    and pt3d_to_2d_fisheye on the shipped solution of jules/run1_1 (oracle/make_golden_shutter.py)."""
+    g = _load(golden_dir, "shutter_ref.npz")
+    clip = _load(golden_dir, "clip_jules_run1_1.npz")
+    cl, cv = kinematics.marker_chains(g["lengths"], g["radii"])
+    N, C = clip["detections"].shape[:2]
+    meas = np.concatenate([clip["detections"].astype(float), np.ones((N, C, 24, 1))], -1)[:, :, :, None, :]
+    pb = cost.Problem(meas=meas, cams=clip["cams"], chain_link=cl, chain_vec=cv, h=1 / float(clip["fps"]))
+    r = cost.residuals(pb, clip["q"], g["tau"], clip["dq"][:, 0:3], clip["ddq"][:, 0:3])[g["frames"], :, :, 0, :]
+    assert (np.abs(r - g["slack"]) / np.maximum(np.abs(g["slack"]), 1.0)).max() < 1e-9
+    # tau = 0 is the undelayed model, and camera 1 (tau fixed at 0, acinoset_misc.py:274-275) is untouched
+    r0 = cost.residuals(pb, clip["q"])[g["frames"], :, :, 0, :]
+    assert np.array_equal(r[:, 0], r0[:, 0]) and np.abs(r[:, 1:] - r0[:, 1:]).max() > 1.0
+    # d slack / d tau against a central difference
+    J = cost.shutter_jacobian(pb, clip["q"], g["tau"], clip["dq"][:, 0:3], clip["ddq"][:, 0:3])
+    eps = 1e-7
+    for c in (1, 4):
+        d = np.zeros(C)
+        d[c] = eps
+        fd = (cost.residuals(pb, clip["q"], g["tau"] + d, clip["dq"][:, 0:3], clip["ddq"][:, 0:3])
+              - cost.residuals(pb, clip["q"], g["tau"] - d, clip["dq"][:, 0:3], clip["ddq"][:, 0:3]))[:, :, :, 0, :] / (2 * eps)
+        assert np.abs(fd[:, c] - J[:, c]).max() <= 1e-6 * np.abs(J[:, c]).max()
+        assert np.abs(np.delete(fd, c, axis=1)).max() == 0.0
