@@ -57,10 +57,15 @@ struct EvalParams {
     int wbytes;             // bytes of one warp's shared slice
     int off_warp;           // byte offset of the first warp slice (after the camera rows)
     double ea, eb, ec;      // exp(loss_a), exp(loss_b), exp(loss_c)
+    double icb;             // 1 / (loss_c - loss_b)
 };
 
 // per-warp FP64 slice (doubles): q, sin/cos, rotations
 constexpr int QO = 0, SCO = 56, RO = 160, WD = 314;
+// compact FP64 layout (WPC = 7, 4 CTAs / SM = 28 warps): the marker offsets and camera translations, which are only
+// written at the very end of phase C, move into doubles that are dead by then -- pos behind the phase-D projection
+// derivatives ([248, 320): the tail of the rotations), tc over q ([0, 24)) -- and the T slice holds U alone
+constexpr int WD_C = 320, POS_C = 248;
 // per-warp T slice (elements): marker offsets, camera translations, U = 3x3 blocks padded to 10 (block 0 = identity,
 // block 1 + k = dR/d(phi,theta,psi) . v of (marker, link) pair k); the f32 flavour also keeps a float copy of sin/cos
 // in front.  The d(u,v)/d(point) rows of the 32 pairs of a round (6 T each) reuse the sin/cos + rotation doubles,
@@ -76,20 +81,28 @@ __device__ __forceinline__ float2 mk2(float a, float b) { return make_float2(a, 
 __device__ __forceinline__ double r_exp(double x) { return exp(x); }
 __device__ __forceinline__ float r_exp(float x) { return expf(x); }
 
-// Redescending loss value only (acinoset_misc.py:2001-2015); one exp and one division per residual.
+// Redescending loss (acinoset_misc.py:2001-2015), value only: sigma(E - s) = 1 / (1 + exp(s) exp(-E)) needs one exp per
+// residual.  Both (u, v) residuals of one detection at once: ONE division serves both (1 / (P_u P_v), P = da db dc <= 2.2e14
+// each, so the product stays far inside the range of either type) and (c - E) / (c - b) is a multiplication by the
+// host-side reciprocal -- 2 divisions and 2 exps per detection instead of 6 and 2.
 template <typename T>
-__device__ __forceinline__ T redescending_value(T E, T a, T b, T c, T ea, T eb, T ec) {
-    const T t = r_exp(-E);
-    const T da = T(1) + t * ea, db = T(1) + t * eb, dc = T(1) + t * ec;
-    const T dab = da * db;
-    const T inv = T(1) / (dab * dc);
-    const T sa = inv * (db * dc), sb = inv * (da * dc), sc = inv * dab;
+__device__ __forceinline__ T redescending_pair(T Eu, T Ev, T a, T b, T c, T icb, T ea, T eb, T ec) {
+    const T tu = r_exp(-Eu), tv = r_exp(-Ev);
+    const T dau = T(1) + tu * ea, dbu = T(1) + tu * eb, dcu = T(1) + tu * ec;
+    const T dav = T(1) + tv * ea, dbv = T(1) + tv * eb, dcv = T(1) + tv * ec;
+    const T dabu = dau * dbu, dabv = dav * dbv;
+    const T Pu = dabu * dcu, Pv = dabv * dcv;
+    const T inv = T(1) / (Pu * Pv);
+    const T iu = inv * Pv, iv = inv * Pu;
+    const T sau = iu * (dbu * dcu), sbu = iu * (dau * dcu), scu = iu * dabu;
+    const T sav = iv * (dbv * dcv), sbv = iv * (dav * dcv), scv = iv * dabv;
     const T cb = c - b;
-    const T p2 = a * E - T(0.5) * a * a;
-    const T qq = (c - E) / cb;
-    const T p3 = a * b - T(0.5) * a * a + (T(0.5) * a * cb) * (T(1) - qq * qq);
-    const T k4 = a * b - T(0.5) * a * a + T(0.5) * a * cb;
-    return (T(1) - sa) * T(0.5) * E * E + (sa - sb) * p2 + (sb - sc) * p3 + sc * k4;
+    const T k2 = T(0.5) * a * a, k3 = a * b - k2, hk = T(0.5) * a * cb, k4 = k3 + hk;
+    const T qu = (c - Eu) * icb, qv = (c - Ev) * icb;
+    const T p3u = k3 + hk * (T(1) - qu * qu), p3v = k3 + hk * (T(1) - qv * qv);
+    const T ru = (T(1) - sau) * T(0.5) * Eu * Eu + (sau - sbu) * (a * Eu - k2) + (sbu - scu) * p3u + scu * k4;
+    const T rv = (T(1) - sav) * T(0.5) * Ev * Ev + (sav - sbv) * (a * Ev - k2) + (sbv - scv) * p3v + scv * k4;
+    return ru + rv;
 }
 
 template <typename T, bool JAC, int WPC, int MINB>
@@ -97,6 +110,7 @@ __global__ void __launch_bounds__(WPC * 32, MINB) eval_kernel(const __grid_const
     using T2 = typename Vec<T>::t2;
     constexpr bool F64 = sizeof(T) == 8;
     constexpr int TS0 = F64 ? 0 : 104;                     // f32: float copy of sin/cos in front of the T slice
+    constexpr bool CMP = F64 && WPC == 7;                  // compact layout (see WD_C)
     extern __shared__ __align__(16) unsigned char smraw[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int N = p.b.N, C = p.b.C, W = p.b.W, TPF = p.TPF;
@@ -111,14 +125,20 @@ __global__ void __launch_bounds__(WPC * 32, MINB) eval_kernel(const __grid_const
         camd[i] = v;
         if (!F64) camt[i] = (T)v;
     }
-    if (JAC) for (int i = tid; i < p.nitem; i += WPC * 32) coltab[i] = p.m.col_item[i];
+    int32_t *goff = coltab - 28;                           // [25] first Jacobian item of marker l: l + u_off[l] / 3
+    if (JAC) {
+        for (int i = tid; i < p.nitem; i += WPC * 32) coltab[i] = p.m.col_item[i];
+        if (tid < 25) goff[tid] = tid + p.m.u_off[tid] / 3;
+    }
     __syncthreads();                                       // the only CTA-wide barrier
     const int nf = p.b.n_frames[s];
     if (k >= nf) return;
     double *wd = reinterpret_cast<double *>(smraw + p.off_warp + warp * p.wbytes);
-    T *wt = reinterpret_cast<T *>(wd + WD);
+    T *wt = reinterpret_cast<T *>(wd + (CMP ? WD_C : WD));
     const T *sct = F64 ? reinterpret_cast<const T *>(wd + SCO) : wt;
-    T *pos = wt + TS0 + T_POS, *tcv = wt + TS0 + T_TC, *U = wt + TS0 + T_U;
+    T *pos = CMP ? reinterpret_cast<T *>(wd + POS_C) : wt + TS0 + T_POS;
+    T *tcv = CMP ? reinterpret_cast<T *>(wd + QO) : wt + TS0 + T_TC;
+    T *U = CMP ? wt : wt + TS0 + T_U;
     T *dp = reinterpret_cast<T *>(wd + SCO);               // [32][6] per-round projection derivatives (phase D)
     const int fi = s * N + k;                              // global frame index
     const int n_ineq = p.m.n_ineq;
@@ -162,6 +182,7 @@ __global__ void __launch_bounds__(WPC * 32, MINB) eval_kernel(const __grid_const
                 for (int i = 0; i < 9; ++i) u[i] = o[i];
             }
         }
+        double px = 0.0, py = 0.0, pz = 0.0, tcr = 0.0;   // written to shared memory after the last read of q and R
         if (lane < 24) {
             // marker offset from the base origin (FP64 accumulate; the FP32 flavour never sees world metres)
             const int l = lane;
@@ -178,7 +199,7 @@ __global__ void __launch_bounds__(WPC * 32, MINB) eval_kernel(const __grid_const
                     z += Rl[6] * v0 + Rl[7] * v1 + Rl[8] * v2;
                 }
             }
-            pos[l * 3 + 0] = (T)x; pos[l * 3 + 1] = (T)y; pos[l * 3 + 2] = (T)z;
+            px = x; py = y; pz = z;
             if (p.eo.pose) {
                 double *o = p.eo.pose + ((size_t)fi * 24 + l) * 3;
                 o[0] = wd[QO + 0] + x; o[1] = wd[QO + 1] + y; o[2] = wd[QO + 2] + z;
@@ -197,7 +218,7 @@ __global__ void __launch_bounds__(WPC * 32, MINB) eval_kernel(const __grid_const
                 by = by + vb[1] * tau + ab[1] * (tau * tau);
                 bz = bz + vb[2] * tau + ab[2] * (tau * tau);
             }
-            tcv[lane] = (T)(cm[8 + 3 * r] * bx + cm[9 + 3 * r] * by + cm[10 + 3 * r] * bz + cm[17 + r]);
+            tcr = cm[8 + 3 * r] * bx + cm[9 + 3 * r] * by + cm[10 + 3 * r] * bz + cm[17 + r];
         }
         if (lane < 26) {
             const int e = lane;
@@ -232,6 +253,9 @@ __global__ void __launch_bounds__(WPC * 32, MINB) eval_kernel(const __grid_const
                 }
             }
         }
+        if (CMP) __syncwarp();                             // pos / tc overwrite the rotations / q
+        if (lane < 24) { pos[lane * 3 + 0] = (T)px; pos[lane * 3 + 1] = (T)py; pos[lane * 3 + 2] = (T)pz; }
+        if (lane < 3 * C) tcv[lane] = (T)tcr;
     }
     __syncwarp();
 
@@ -239,7 +263,7 @@ __global__ void __launch_bounds__(WPC * 32, MINB) eval_kernel(const __grid_const
     T rho = T(0);
     {
         const T la_ = (T)p.b.loss_a, lb_ = (T)p.b.loss_b, lc_ = (T)p.b.loss_c;
-        const T ea = (T)p.ea, eb = (T)p.eb, ec = (T)p.ec;
+        const T ea = (T)p.ea, eb = (T)p.eb, ec = (T)p.ec, icb = (T)p.icb;
         for (int p0 = 0; p0 < TPF; p0 += 32) {
             const int pi = p0 + lane;
             MeasRaw nxt;
@@ -270,8 +294,7 @@ __global__ void __launch_bounds__(WPC * 32, MINB) eval_kernel(const __grid_const
                     if (sq) {
                         rho += (wgt * ru) * (wgt * ru) + (wgt * rv) * (wgt * rv);
                     } else {
-                        rho += redescending_value<T>(fabs(wgt * ru), la_, lb_, lc_, ea, eb, ec);
-                        rho += redescending_value<T>(fabs(wgt * rv), la_, lb_, lc_, ea, eb, ec);
+                        rho += redescending_pair<T>(fabs(wgt * ru), fabs(wgt * rv), la_, lb_, lc_, icb, ea, eb, ec);
                     }
                 }
                 if (JAC) {
@@ -288,11 +311,11 @@ __global__ void __launch_bounds__(WPC * 32, MINB) eval_kernel(const __grid_const
                 const int nitem = p.nitem;
                 const int pe = min(p0 + 32, TPF);
                 const int c0 = p0 / 24, l0 = p0 - 24 * c0;
-                const int g0 = c0 * nitem + l0 + p.m.u_off[l0] / 3;
+                const int g0 = c0 * nitem + goff[l0];
                 int g1 = C * nitem;
                 if (pe < TPF) {
                     const int c1 = pe / 24, l1 = pe - 24 * c1;
-                    g1 = c1 * nitem + l1 + p.m.u_off[l1] / 3;
+                    g1 = c1 * nitem + goff[l1];
                 }
                 T2 *jb = reinterpret_cast<T2 *>(p.eo.jac) + (size_t)fi * C * 3 * nitem;
                 for (int g = g0 + lane; g < g1; g += 32) {
@@ -338,6 +361,7 @@ static int eval_cfg() {
     if (cfg < 0) {
         const char *e = getenv("CPE_EVAL_CFG");      // tuning knob for experiments; default chosen by measurement
         cfg = e ? atoi(e) : 1;      // 1: 6 CTAs/SM (80 regs) for FP64, 8 CTAs/SM (64 regs) for FP32
+                                    // 3: FP64 compact layout, 7 warps / CTA x 4 CTAs / SM (72 regs); FP32 as 1
     }
     return cfg;
 }
@@ -353,11 +377,14 @@ static int launch_eval(const cpe_model *model, const cpe_batch *b, const double 
     if (!model->u_off || !model->u_item) return CPE_E_NULL;
     if ((b->shutter_tau || b->base_dq || b->base_ddq) && !(b->shutter_tau && b->base_dq && b->base_ddq)) return CPE_E_NULL;
     constexpr bool f64 = sizeof(T) == 8;
-    constexpr int WPC = 4;
+    const int cfg = eval_cfg();
+    const bool cmp = f64 && cfg == 3;                    // compact layout: 7 warps / CTA
+    const int WPC = cmp ? 7 : 4;
     const bool jac = eo->jac != nullptr;
     EvalParams p;
     p.m = *model; p.b = *b; p.q = q; p.eo = *eo;
     p.ea = exp(b->loss_a); p.eb = exp(b->loss_b); p.ec = exp(b->loss_c);
+    p.icb = 1.0 / (b->loss_c - b->loss_b);
     p.TPF = b->C * 24;
     p.chunks = (b->N + WPC - 1) / WPC;
     p.n_u = model->n_u;
@@ -365,23 +392,23 @@ static int launch_eval(const cpe_model *model, const cpe_batch *b, const double 
     p.nitem = 24 + p.n_pair;
     p.item_magic = ((1u << 24) + p.nitem - 1) / p.nitem;
     if (jac && !model->col_item) return CPE_E_NULL;
-    const int t_elems = (f64 ? 0 : 104) + T_U + 10 + 10 * p.n_pair;
-    p.wbytes = (int)((WD * sizeof(double) + t_elems * sizeof(T) + 15) & ~(size_t)15);
+    const int t_elems = cmp ? 10 + 10 * p.n_pair : (f64 ? 0 : 104) + T_U + 10 + 10 * p.n_pair;
+    p.wbytes = (int)(((cmp ? WD_C : WD) * sizeof(double) + t_elems * sizeof(T) + 15) & ~(size_t)15);
     p.off_warp = (int)(b->C * CPE_CAM_STRIDE * (sizeof(double) + (f64 ? 0 : sizeof(T))) +
-                       sizeof(int32_t) * ((p.nitem + 3) & ~3));
+                       sizeof(int32_t) * (28 + ((p.nitem + 3) & ~3)));
     const size_t smem = (size_t)p.off_warp + (size_t)WPC * p.wbytes;
     const long long grid_ll = (long long)b->S * p.chunks;
     if (grid_ll > 0x7fffffffLL) return CPE_E_DIM;
     const int grid = (int)grid_ll;
-    const int cfg = eval_cfg();
     if constexpr (f64) {
-        if (cfg == 0) return jac ? launch_cfg<T, true, WPC, 7>(p, grid, smem, st) : launch_cfg<T, false, WPC, 7>(p, grid, smem, st);
-        if (cfg == 2) return jac ? launch_cfg<T, true, WPC, 5>(p, grid, smem, st) : launch_cfg<T, false, WPC, 5>(p, grid, smem, st);
-        return jac ? launch_cfg<T, true, WPC, 6>(p, grid, smem, st) : launch_cfg<T, false, WPC, 6>(p, grid, smem, st);
+        if (cfg == 3) return jac ? launch_cfg<T, true, 7, 4>(p, grid, smem, st) : launch_cfg<T, false, 7, 4>(p, grid, smem, st);
+        if (cfg == 0) return jac ? launch_cfg<T, true, 4, 7>(p, grid, smem, st) : launch_cfg<T, false, 4, 7>(p, grid, smem, st);
+        if (cfg == 2) return jac ? launch_cfg<T, true, 4, 5>(p, grid, smem, st) : launch_cfg<T, false, 4, 5>(p, grid, smem, st);
+        return jac ? launch_cfg<T, true, 4, 6>(p, grid, smem, st) : launch_cfg<T, false, 4, 6>(p, grid, smem, st);
     } else {
-        if (cfg == 0) return jac ? launch_cfg<T, true, WPC, 10>(p, grid, smem, st) : launch_cfg<T, false, WPC, 10>(p, grid, smem, st);
-        if (cfg == 2) return jac ? launch_cfg<T, true, WPC, 12>(p, grid, smem, st) : launch_cfg<T, false, WPC, 12>(p, grid, smem, st);
-        return jac ? launch_cfg<T, true, WPC, 8>(p, grid, smem, st) : launch_cfg<T, false, WPC, 8>(p, grid, smem, st);
+        if (cfg == 0) return jac ? launch_cfg<T, true, 4, 10>(p, grid, smem, st) : launch_cfg<T, false, 4, 10>(p, grid, smem, st);
+        if (cfg == 2) return jac ? launch_cfg<T, true, 4, 12>(p, grid, smem, st) : launch_cfg<T, false, 4, 12>(p, grid, smem, st);
+        return jac ? launch_cfg<T, true, 4, 8>(p, grid, smem, st) : launch_cfg<T, false, 4, 8>(p, grid, smem, st);
     }
 }
 
