@@ -156,7 +156,8 @@ def init_trajectory(root_dir: str,
     if not kinematic_model:
         raise NotImplementedError("kinetic (physics-based) model: out of scope of this path (SURVEY.md section 8f.3)")
     if shutter_delay_estimation:
-        raise NotImplementedError("shutter-delay estimation is not on this path (SURVEY.md section 8f.4)")
+        raise NotImplementedError("shutter-delay estimation is not on this path (SURVEY.md section 8f.4); the delay term "
+                                  "itself is evaluated by cpe_eval_* (cpe_batch.shutter_tau), see DESIGN.md section 10")
     if cheetah_name not in ("jules", "phantom", "shiraz", "arabia"):
         cheetah_name = "acinoset"
     ground_plane_height = 0.0

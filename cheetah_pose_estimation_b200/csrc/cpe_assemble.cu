@@ -31,7 +31,7 @@ struct AsmParams {
     cpe_assemble_out ao;
     int TPF;        // C * 24
     int at_size;    // doubles of the aliased region (per-task blocks, then entries + group scratch)
-    double ea, eb, ec;
+    double ea, eb, ec, icb;     // exp(loss_a), exp(loss_b), exp(loss_c), 1 / (loss_c - loss_b)
 };
 
 // per-frame shared layout (doubles), after cam[C*24]
@@ -191,17 +191,17 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
             const double wgt = gate * p.m.meas_w[w * 24 + ml] * (sq ? 1.0 : cmult);
             const double eu = wgt * (pr.u - um), ev = wgt * (pr.v - vm);
             const double Eu = fabs(eu), Ev = fabs(ev);
-            double rho, du_, dv_;
+            double du_, dv_, wu_, wv_;
             if (sq) {
                 du_ = 2.0 * Eu; dv_ = 2.0 * Ev;
+                wu_ = Eu > 0.0 ? 2.0 : 0.0; wv_ = Ev > 0.0 ? 2.0 : 0.0;
             } else {
-                redescending(Eu, la_, lb_, lc_, p.ea, p.eb, p.ec, rho, du_);
-                redescending(Ev, la_, lb_, lc_, p.ea, p.eb, p.ec, rho, dv_);
+                redescending_pair_d(Eu, Ev, la_, lb_, lc_, p.icb, p.ea, p.eb, p.ec, du_, dv_, wu_, wv_);
             }
             gu += du_ * (eu > 0.0 ? 1.0 : (eu < 0.0 ? -1.0 : 0.0)) * wgt;
             gv += dv_ * (ev > 0.0 ? 1.0 : (ev < 0.0 ? -1.0 : 0.0)) * wgt;
-            hu += (Eu > 0.0 ? fmax(du_ / Eu, 0.0) : 0.0) * wgt * wgt;
-            hv += (Ev > 0.0 ? fmax(dv_ / Ev, 0.0) : 0.0) * wgt * wgt;
+            hu += wu_ * wgt * wgt;
+            hv += wv_ * wgt * wgt;
         }
         double *ab = AT + tid * 9;
         ab[0] = hu * pr.du[0] * pr.du[0] + hv * pr.dv[0] * pr.dv[0];
@@ -390,6 +390,7 @@ extern "C" int cpe_assemble_f64(const cpe_model *model, const cpe_batch *b, cons
     p.m = *model; p.b = *b; p.q = q; p.damp = damp; p.ao = *out;
     p.TPF = b->C * 24;
     p.ea = exp(b->loss_a); p.eb = exp(b->loss_b); p.ec = exp(b->loss_c);
+    p.icb = 1.0 / (b->loss_c - b->loss_b);
     const int need = ENT_PAD + DDI_SZ + YS_SZ;
     p.at_size = p.TPF * 9 > need ? p.TPF * 9 : need;
     const size_t smem = (size_t)(b->C * CPE_CAM_STRIDE + A_AT + p.at_size) * sizeof(double);

@@ -198,6 +198,43 @@ __device__ __forceinline__ void redescending(double E, double a, double b, doubl
            (sb - sc) * a * (c - E) / cb + dc * k4;
 }
 
+// d rho / dE and the Gauss-Newton curvature weight max(rho'(E) / E, 0) of BOTH residuals of one detection (K2).  All
+// eight divisions of the two redescending() calls and the two rho'/E share ONE reciprocal, 1 / (P_u P_v E_u E_v) with
+// P = (1 + t ea)(1 + t eb)(1 + t ec) <= 2.2e14 (E = 0 is replaced by 1 in the product and its weight set to 0), and
+// (c - E) / (c - b) is a multiplication by icb = 1 / (c - b).
+__device__ __forceinline__ void redescending_pair_d(double Eu, double Ev, double a, double b, double c, double icb,
+                                                    double ea, double eb, double ec, double &du, double &dv,
+                                                    double &wu, double &wv) {
+    const double tu = exp(-Eu), tv = exp(-Ev);
+    const double dau = 1.0 + tu * ea, dbu = 1.0 + tu * eb, dcu = 1.0 + tu * ec;
+    const double dav = 1.0 + tv * ea, dbv = 1.0 + tv * eb, dcv = 1.0 + tv * ec;
+    const double dabu = dau * dbu, dabv = dav * dbv;
+    const double Pu = dabu * dcu, Pv = dabv * dcv;
+    const double Eus = Eu > 0.0 ? Eu : 1.0, Evs = Ev > 0.0 ? Ev : 1.0;
+    const double PP = Pu * Pv, EE = Eus * Evs;
+    const double inv = 1.0 / (PP * EE);
+    const double iP = inv * EE, iE = inv * PP;
+    const double iPu = iP * Pv, iPv = iP * Pu, iEu = iE * Evs, iEv = iE * Eus;
+    const double cb = c - b;
+    const double k2 = 0.5 * a * a, k3 = a * b - k2, hk = 0.5 * a * cb, k4 = k3 + hk;
+    {
+        const double sa = iPu * (dbu * dcu), sb = iPu * (dau * dcu), sc = iPu * dabu;
+        const double da = sa * (1.0 - sa), db = sb * (1.0 - sb), dc = sc * (1.0 - sc);
+        const double q = (c - Eu) * icb;
+        du = -da * 0.5 * Eu * Eu + (1.0 - sa) * Eu + (da - db) * (a * Eu - k2) + (sa - sb) * a +
+             (db - dc) * (k3 + hk * (1.0 - q * q)) + (sb - sc) * a * q + dc * k4;
+        wu = Eu > 0.0 ? fmax(du * iEu, 0.0) : 0.0;
+    }
+    {
+        const double sa = iPv * (dbv * dcv), sb = iPv * (dav * dcv), sc = iPv * dabv;
+        const double da = sa * (1.0 - sa), db = sb * (1.0 - sb), dc = sc * (1.0 - sc);
+        const double q = (c - Ev) * icb;
+        dv = -da * 0.5 * Ev * Ev + (1.0 - sa) * Ev + (da - db) * (a * Ev - k2) + (sa - sb) * a +
+             (db - dc) * (k3 + hk * (1.0 - q * q)) + (sb - sc) * a * q + dc * k4;
+        wv = Ev > 0.0 ? fmax(dv * iEv, 0.0) : 0.0;
+    }
+}
+
 // R = Rz(psi) Ry(theta) Rx(phi) from sc = {sin phi, cos phi, sin theta, cos theta, sin psi, cos psi}
 // (reference shared/physical_education/utils.py:39-64, links.py:483)
 __device__ __forceinline__ void rot_from_sc(const double *sc, double *M) {
