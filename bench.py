@@ -182,7 +182,7 @@ def run_reference(a):
             "gpu_launches": 0,
             "note": "reference = Python+Pyomo/IPOPT, not installable here; timed: numpy FP64 oracle port of its "
                     "FK/projection/redescending-cost functions + analytic Jacobian"}
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -443,8 +443,27 @@ def cpu_baseline_leg(a):
                       f"(residual + cost + dense Jacobian), 1 process; host has {os.cpu_count()} cores"}
 
 
+_JSON_FD = None
+
+
+def _claim_stdout():
+    """The contract is ONE JSON line on stdout.  NCCL (its version banner under NCCL_DEBUG), nvcc and child processes
+    write to file descriptor 1 behind Python's back, so fd 1 is pointed at stderr for the whole run and the JSON line
+    goes to a private duplicate of the original stdout."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def _emit(line):
+    sys.stdout.flush()
+    os.write(_JSON_FD, (json.dumps(line) + "\n").encode())
+
+
 def main():
     a = parse_args()
+    _claim_stdout()
     if a.impl == "reference":
         run_reference(a)
         return
@@ -522,7 +541,7 @@ def main():
             line["grf"] = grf
         if world == 1:
             line["cpu_baseline"] = cpu_baseline_leg(a)
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -119,3 +119,34 @@ def test_sweep_size_properties(gpu):
     dp = sp.lm_step(qp, damp)[0].clone()
     d0 = sv.lm_step(q, damp)[0].clone()
     assert torch.equal(dp, d0[perm])
+
+
+def test_full_sweep_size_wave_split_and_checksum(gpu):
+    """The whole C4 configuration of BASELINE.json -- 4096 sequences x 500 frames x 6 cameras on one GPU (12.3 M
+    frame.views) -- with properties that need no oracle: (i) one launch over all sequences and eight launches over
+    waves of 512 give bit-identical per-sequence costs (a sequence's result does not depend on its batch), (ii) the sum
+    of the wave checksums equals the checksum of the whole, (iii) tiled sequences (the generator repeats 32 base
+    trajectories with fresh noise) have pairwise different measurement costs but identical joint / inequality terms
+    at the shared q, (iv) the FP32 flavour agrees with FP64 to 1e-6 on the measurement cost of every sequence."""
+    import torch
+    from cheetah_pose_estimation_b200 import engine, synthetic
+    S, N, C, WAVE = 4096, 500, 6, 512
+    batch, q_true, _ = synthetic.make_device_problem(S, N, C, seed=0, device="cuda:0", dlc_native=True)
+    q = q_true.contiguous()
+    sv = engine.Solver(gpu, batch, with_solver=False)
+    whole = sv.evaluate(q)["cost"].clone()
+    torch.cuda.synchronize()
+    assert whole.shape == (S, 4) and bool(torch.isfinite(whole).all())
+    parts = []
+    for s0 in range(0, S, WAVE):
+        w = engine.Solver(gpu, batch.window(s0, s0 + WAVE), with_solver=False)
+        parts.append(w.evaluate(q[s0:s0 + WAVE])["cost"].clone())
+    waves = torch.cat(parts)
+    assert torch.equal(waves, whole)
+    chk = torch.stack([p.sum(dim=0) for p in parts]).sum(dim=0)
+    assert bool(((chk - whole.sum(dim=0)).abs() <= 1e-12 * whole.sum(dim=0).abs()).all())
+    # sequences s and s + 32 share trajectory and cameras (q_true) but not the detection noise
+    assert bool((whole[:32, 0] != whole[32:64, 0]).all())
+    assert torch.equal(whole[:32, 2:], whole[32:64, 2:]) and torch.equal(whole[:32, 1], whole[32:64, 1])
+    w32 = sv.evaluate(q, f32=True)["cost"]
+    assert float(((w32[:, 0] - whole[:, 0]).abs() / whole[:, 0].abs()).max()) < 1e-6
