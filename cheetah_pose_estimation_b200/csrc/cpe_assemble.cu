@@ -180,7 +180,16 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
         const double la_ = p.b.loss_a, lb_ = p.b.loss_b, lc_ = p.b.loss_c;
         const double *cm = cam + mc * CPE_CAM_STRIDE;
         Proj pr;
-        project_point<true>(fr + A_POSO + ml * 3, cm, p.b.cam_model, pr);
+        double pt[3] = {fr[A_POSO + ml * 3], fr[A_POSO + ml * 3 + 1], fr[A_POSO + ml * 3 + 2]};
+        if (p.b.shutter_tau) {
+            // shutter delay: camera mc sees the frame displaced by dq tau + ddq tau^2 (acinoset_misc.py:280-286)
+            const double tau = p.b.shutter_tau[(size_t)s * C + mc];
+            const double *vb = p.b.base_dq + fidx * 3, *ab = p.b.base_ddq + fidx * 3;
+            pt[0] += vb[0] * tau + ab[0] * (tau * tau);
+            pt[1] += vb[1] * tau + ab[1] * (tau * tau);
+            pt[2] += vb[2] * tau + ab[2] * (tau * tau);
+        }
+        project_point<true>(pt, cm, p.b.cam_model, pr);
         const double cmult = cm[20];
         double hu = 0.0, hv = 0.0, gu = 0.0, gv = 0.0;
         for (int w = 0; w < W; ++w) {
@@ -215,6 +224,16 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
         ab[8] = gu * pr.du[2] + gv * pr.dv[2];
     }
     __syncthreads();
+    if (p.ao.cam_blocks) {
+        // per camera: sum over markers of the point-space curvature (6) and gradient (3) -- what the shutter-delay
+        // unknowns see (d slack / d tau_c and the cross-frame base terms are d(u,v)/d(point) times a 3-vector)
+        for (int i = tid; i < C * 9; i += nt) {
+            const int c = i / 9, comp = i - c * 9;
+            double v = 0.0;
+            for (int l = 0; l < 24; ++l) v += AT[(c * 24 + l) * 9 + comp];
+            p.ao.cam_blocks[(fidx * C + c) * 9 + comp] = v;
+        }
+    }
     // ---- A_l = sum over cameras (fixed order), expanded to full 3x3 columns in B space; b_l ------------------------
     for (int i = tid; i < 216; i += nt) {
         const int l = i / 9, comp = i - l * 9;
@@ -385,7 +404,7 @@ extern "C" int cpe_assemble_f64(const cpe_model *model, const cpe_batch *b, cons
         !model->s_items || !model->ent_order || !model->s_order)
         return CPE_E_NULL;
     if (out->S && (!damp || !out->ghat || !out->Y || !out->y)) return CPE_E_NULL;
-    if (b->shutter_tau || b->base_dq || b->base_ddq) return CPE_E_ARG;   // delay estimation is not on the LM path (cpe.h)
+    if ((b->shutter_tau || b->base_dq || b->base_ddq) && !(b->shutter_tau && b->base_dq && b->base_ddq)) return CPE_E_NULL;
     AsmParams p;
     p.m = *model; p.b = *b; p.q = q; p.damp = damp; p.ao = *out;
     p.TPF = b->C * 24;

@@ -294,6 +294,8 @@ class Solver:
         if reduced:
             ao.S, ao.ghat, ao.Y, ao.y = (self.Sblk.data_ptr(), self.ghat.data_ptr(), self.Y.data_ptr(), self.y.data_ptr())
         ao.g, ao.diagH = self.g.data_ptr(), self.diagH.data_ptr()
+        if hasattr(self, "cam_blocks"):
+            ao.cam_blocks = self.cam_blocks.data_ptr()
         if raw is not None:
             ao.Hraw = raw.data_ptr()
         return ao
@@ -431,6 +433,132 @@ class Solver:
         if self.priors is not None:
             res["prior_cost"] = out["prior_cost"].clone()
         self.result = res
+
+
+    # ---- shutter-delay estimation (acinoset_misc.py:182-183, 273-286) ------------------------------------
+    def set_delay(self, q, tau):
+        """Point the batch at the delay tau[S,C] and at the base velocity / acceleration of q (base_rates)."""
+        v, a = base_rates(q[..., 0:3], self.b.h)
+        self.b.shutter_tau, self.b.base_dq, self.b.base_ddq = tau.contiguous(), v.contiguous(), a.contiguous()
+
+    def delay_terms(self, q, tau):
+        """From the per-camera blocks of the last `assemble` at (q, tau): the part of d cost / d q that goes through
+        dq_base and ddq_base (g_extra[S,N,3], on the base x, y, z of frames n, n-1, n-2), d cost / d tau [S,C], and the
+        Gauss-Newton curvature of tau [S,C] (cameras do not share residuals, so it is diagonal)."""
+        blk = self.cam_blocks                                                  # [S,N,C,9]
+        bx = q[..., 0:3].detach().clone().requires_grad_(True)
+        tv = tau.detach().clone().requires_grad_(True)
+        v, a = base_rates(bx, self.b.h)
+        d = v[:, :, None, :] * tv[:, None, :, None] + a[:, :, None, :] * (tv * tv)[:, None, :, None]
+        (blk[..., 6:9] * d).sum().backward()
+        w = (v[:, :, None, :] + 2.0 * tv[:, None, :, None] * a[:, :, None, :]).detach()          # d d / d tau, [S,N,C,3]
+        A = blk[..., 0:6]
+        curv = (A[..., 0] * w[..., 0] ** 2 + A[..., 3] * w[..., 1] ** 2 + A[..., 5] * w[..., 2] ** 2
+                + 2.0 * (A[..., 1] * w[..., 0] * w[..., 1] + A[..., 2] * w[..., 0] * w[..., 2]
+                         + A[..., 4] * w[..., 1] * w[..., 2])).sum(dim=1)
+        return bx.grad, tv.grad, curv
+
+    def assemble_delayed(self, q, tau, damp, reduced=True):
+        """`assemble` at (q, tau) with the exact gradient: K2 gives d cost / d q_n at fixed dq, ddq; the terms through
+        dq_base / ddq_base are added to the gradient (they only touch base x, y, z, which are not eliminated, so the
+        reduced gradient takes them unchanged).  Returns (g_tau, curv_tau)."""
+        self.set_delay(q, tau)
+        if not hasattr(self, "cam_blocks"):
+            self.cam_blocks = torch.zeros(self.b.S, self.b.N, self.b.C, 9, dtype=torch.float64, device=q.device)
+            self._xyz_ind = torch.as_tensor(np.asarray(self.m.tables["ind_pos"][0:3], np.int64), device=q.device)
+            assert int(self._xyz_ind.min()) >= 0
+        self.assemble(q, damp, reduced=reduced)
+        g_extra, g_tau, curv = self.delay_terms(q, tau)
+        self.g[..., 0:3] += g_extra
+        if reduced:
+            self.ghat[..., self._xyz_ind] += g_extra
+        return g_tau, curv
+
+    def solve_shutter(self, q0, tau0=None, max_iter=40, n_outer=4, damp0=1e-3, ftol=1e-7,
+                      mu_schedule=(1e4, 1e5, 1e6, 1e6), fix_first=True):
+        """Multi-view reconstruction WITH shutter-delay estimation (`shutter_delay_estimation=True`): minimises the same
+        objective as `solve` over q and the per-camera delays tau[S,C] (camera 1 fixed at 0, |tau| <= 1/fps, as
+        acinoset_misc.py:183, 274-275).  Each LM iteration takes ONE joint step from one assembly at (q, tau): the
+        band solve for q with the exact gradient (assemble_delayed) and a damped scalar Newton step per camera for tau,
+        accepted or rejected together on the true cost.  The Hessian is block diagonal in (q, tau) and frame local in q
+        (the coupling of frame n to n-1, n-2 through dq, ddq is in the gradient only): the stationary point is exact,
+        the convergence rate degrades as |tau| approaches 1/fps.  Returns the dict of `solve` plus `tau`."""
+        b, lib = self.b, self.lib
+        assert self.priors is None
+        S, N, Cn, dev = b.S, b.N, b.C, q0.device
+        q = q0.clone().contiguous()
+        tau = torch.zeros(S, Cn, dtype=torch.float64, device=dev) if tau0 is None else tau0.clone()
+        lim = b.h[:, None].expand(S, Cn)
+        b.lam_eq = torch.zeros(S, N, 26, dtype=torch.float64, device=dev)
+        b.lam_in = torch.zeros(S, N, self.m.n_ineq, dtype=torch.float64, device=dev)
+        b.active = None
+        self.state.zero_()
+        self.state[1].fill_(damp0)
+        self.state[2].fill_(2.0)
+        self.counters.zero_()
+        cost_try = torch.zeros(S, 4, dtype=torch.float64, device=dev)
+        damp = self.state[1]
+        total_inner = 0
+        for outer in range(n_outer):
+            b.mu_eq = b.mu_in = float(mu_schedule[min(outer, len(mu_schedule) - 1)])
+            self.set_delay(q, tau)
+            self.evaluate(q)
+            self.state[0].copy_(self.cost.sum(dim=1))
+            self.active.fill_(1)
+            for it in range(max_iter):
+                g_tau, curv = self.assemble_delayed(q, tau, damp)
+                self.band_solve()
+                self.step_apply(q, damp)
+                step = -g_tau / (curv * (1.0 + damp[:, None]) + 1e-300)
+                step = torch.where(curv > 0, step, torch.zeros_like(step))
+                tau_try = torch.minimum(torch.maximum(tau + step, -lim), lim)
+                if fix_first:
+                    tau_try[:, 0] = tau[:, 0]
+                self.set_delay(self.q_try, tau_try)
+                self.evaluate(self.q_try, cost_out=cost_try)
+                n_acc = self.counters[:, 1].clone()
+                bs = b.struct()
+                _lib.check(lib.cpe_step_accept_f64(C.byref(bs), _ptr(cost_try), _ptr(self.frame_pred), _ptr(q),
+                                                   _ptr(self.q_try), _ptr(self.state), _ptr(self.counters),
+                                                   _ptr(self.active), C.c_double(ftol), _stream()), "cpe_step_accept_f64")
+                self.launches += 1
+                accepted = self.counters[:, 1] > n_acc
+                tau = torch.where(accepted[:, None], tau_try, tau)
+                total_inner += 1
+                if not bool(self.active.any()):
+                    break
+            self.set_delay(q, tau)
+            self.evaluate(q, constraints=True)
+            bs = b.struct()
+            _lib.check(lib.cpe_update_multipliers_f64(C.byref(self.m.struct), C.byref(bs), _ptr(self.c_eq), _ptr(self.v_in),
+                                                      _ptr(b.lam_eq), _ptr(b.lam_in), _stream()),
+                       "cpe_update_multipliers_f64")
+            self.launches += 1
+        self.set_delay(q, tau)
+        out = self.evaluate(q, constraints=True)
+        self.result = dict(q=q, tau=tau, cost=out["cost"].clone(), c_eq=out["c_eq"], v_in=out["v_in"],
+                           counters=self.counters.clone(), status=self.status.clone(), lockstep_iterations=total_inner)
+        return self.result
+
+
+def base_rates(bxyz, h, n_frames=None):
+    """dq_base, ddq_base [S,N,3] of the q-only formulation: the reference's implicit-Euler collocation
+    (collocation.py:58-68: q_n = q_{n-1} + h dq_n, dq_n = dq_{n-1} + h ddq_n) eliminated, i.e. backward differences of
+    the base x, y, z.  The reference leaves dq_1 and ddq_1 (hence ddq_2) free; with them eliminated there is nothing
+    left to define them, so they are continued constantly: dq_0 = dq_1, ddq_0 = ddq_1 = ddq_2 (a deviation from the
+    reference NLP confined to the first two frames, stated in DESIGN.md).  Plain differentiable torch ops on [S,N,3]."""
+    S, N, _ = bxyz.shape
+    hh = h[:, None, None]
+    if N < 2:
+        z = torch.zeros_like(bxyz)
+        return z, z
+    v1 = (bxyz[:, 1:] - bxyz[:, :-1]) / hh                                   # frames 1..N-1
+    v = torch.cat([v1[:, :1], v1], dim=1)
+    if N < 3:
+        return v, torch.zeros_like(bxyz)
+    a2 = (v1[:, 1:] - v1[:, :-1]) / hh                                       # frames 2..N-1
+    a = torch.cat([a2[:, :1], a2[:, :1], a2], dim=1)
+    return v, a
 
 
 def shutter_jacobian(jac, batch):

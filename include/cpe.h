@@ -130,10 +130,11 @@ typedef struct cpe_batch {
                                        (their outputs keep their previous contents) -- converged sequences of an LM loop */
     /* Shutter delay of the measurement model (acinoset_misc.py:182-183, 273-286; acinoset_opt.py:342-352): camera c sees
        every marker of frame n displaced by  dq_base[n] tau_c + ddq_base[n] tau_c^2  (no 1/2, as in the reference).
-       All three NULL = no delay.  cpe_eval_* honours them (residuals, costs, Jacobian d slack / d q_n at fixed dq, ddq,
-       tau -- the reference's own partial derivative, dq and ddq being separate NLP variables there; eo.pose stays the
-       undelayed FK, the reference's `positions`).  cpe_assemble_f64 (the LM normal equations) returns
-       CPE_E_ARG when a delay is set: estimating tau is not on this path yet. */
+       All three NULL = no delay.  cpe_eval_* and cpe_assemble_f64 honour them: residuals, costs, and derivatives with
+       respect to q_n at fixed dq, ddq, tau -- the reference's own partial derivatives, dq and ddq being separate NLP
+       variables there; eo.pose stays the undelayed FK, the reference's `positions`.  The derivatives with respect to
+       tau, dq_base and ddq_base come from cpe_assemble_out.cam_blocks (engine.Solver.solve_shutter is the driver that
+       estimates tau with them). */
     const double *shutter_tau;      /* [S,C] seconds; the reference fixes camera 1 at 0 and bounds the rest by +-1/fps */
     const double *base_dq;          /* [S,N,3] velocity of base x, y, z     (robot["base"]["dq"][n, 1, .]) */
     const double *base_ddq;         /* [S,N,3] acceleration of base x, y, z (robot["base"]["ddq"][n, 1, .]) */
@@ -171,6 +172,10 @@ typedef struct cpe_assemble_out {
     double *g;                      /* [S,N,54] full gradient (incl. motion gradient) */
     double *diagH;                  /* [S,N,54] diag of the undamped GN Hessian incl. motion diagonal */
     double *Hraw;                   /* optional [S,N,54,54] dense undamped frame Hessian (tests / cpe_normal_eq) */
+    double *cam_blocks;             /* optional [S,N,C,9] per camera, summed over markers and hypotheses, in point space:
+                                       IRLS-weighted P^T P (xx, xy, xz, yy, yz, zz) and P^T rho' (x, y, z), P = d(u,v)/d(point).
+                                       The shutter-delay terms are built from these: d cost / d tau_c =
+                                       sum_n b_nc . (dq_base + 2 tau_c ddq_base), and the gradient through dq_base, ddq_base */
 } cpe_assemble_out;
 
 /* Data-driven monocular priors on the reduced pose x = Tr q_ind (28 = the coordinates with a motion prior; the

@@ -99,6 +99,32 @@ def delayed_pose(pb: Problem, q, tau=None, dq_base=None, ddq_base=None):
     return pose[:, None, :, :] + off[:, :, None, :]
 
 
+def base_rates(q, h):
+    """dq_base, ddq_base [N,3] once the collocation rows (collocation.py:58-68) are eliminated: backward differences
+    of the base x, y, z.  The reference keeps dq_1 and ddq_1 (hence ddq_2) as free variables; in the q-only
+    formulation they are continued constantly, dq_0 = dq_1 and ddq_0 = ddq_1 = ddq_2 (stated deviation, first two
+    frames only)."""
+    b = np.asarray(q, float)[:, 0:3]
+    N = b.shape[0]
+    v, a = np.zeros_like(b), np.zeros_like(b)
+    if N >= 2:
+        v[1:] = (b[1:] - b[:-1]) / h
+        v[0] = v[1]
+    if N >= 3:
+        a[2:] = (v[2:] - v[1:-1]) / h
+        a[0] = a[1] = a[2]
+    return v, a
+
+
+def delayed_cost_terms(pb: Problem, q, tau, lam_eq=None, lam_in=None):
+    """cost_terms of the problem WITH shutter-delay estimation: the measurement term sees
+    pose + dq_base(q) tau_c + ddq_base(q) tau_c^2 with the rates of base_rates."""
+    v, a = base_rates(q, pb.h)
+    t = cost_terms(pb, q, lam_eq, lam_in)
+    t[0] = measurement_cost(pb, q, tau, v, a)
+    return t
+
+
 def residuals(pb: Problem, q, tau=None, dq_base=None, ddq_base=None):
     """slack[N,C,L,W,2] = proj(pose [+ shutter-delay displacement]) - meas  (what the reference saves as `meas_err`)."""
     pts = delayed_pose(pb, q, tau, dq_base, ddq_base)                        # [N,C,24,3]

@@ -386,10 +386,9 @@ def test_square_loss_mode_matches_oracle(gpu):
 def test_shutter_delay_evaluation(gpu, golden_dir):
     """Shutter-delay term of the measurement model (acinoset_misc.py:273-288): K1's residuals, cost and Jacobian with
     per-camera delays against the oracle and against the reference-function golden; d slack / d tau from the packed
-    Jacobian; the LM normal equations refuse a delayed batch (estimating tau is not on this path)."""
-    import ctypes as C
+    Jacobian (the estimation of the delays is tested below)."""
     import torch
-    from cheetah_pose_estimation_b200 import _lib, engine, skeleton
+    from cheetah_pose_estimation_b200 import engine, skeleton
     from oracle import cameras, cost, kinematics, tables
     g = np.load(os.path.join(golden_dir, "shutter_ref.npz"))
     clip = np.load(os.path.join(golden_dir, "clip_jules_run1_1.npz"))
@@ -450,11 +449,89 @@ def test_shutter_delay_evaluation(gpu, golden_dir):
                             with_solver=False).evaluate(qd, resid=True, f32=True)
     torch.cuda.synchronize()
     assert np.abs(out32_0["resid"][:, :, 1:, :, 0, :].cpu().numpy() - r32[:, :, 1:]).max() > 1.0   # the delay did act
-    # the LM assembly refuses a delayed batch loudly
-    ao = _lib.CpeAssembleOut()
-    gbuf = torch.zeros(2, N, 54, **dev)
-    dbuf = torch.zeros(2, N, 54, **dev)
-    ao.g, ao.diagH = gbuf.data_ptr(), dbuf.data_ptr()
-    bs = batch.struct()
-    rc = gpu.lib.cpe_assemble_f64(C.byref(gpu.struct), C.byref(bs), C.c_void_p(qd.data_ptr()), None, C.byref(ao), None)
-    assert rc == -1
+
+
+def _delayed_problem(S, N, C, seed, tau_scale, noise=1.0):
+    """Synthetic sequences whose detections follow the delayed measurement model exactly (oracle.delayed_pose with
+    the q-only rates) plus Gaussian pixel noise; returns (prob, tau_true[S,C])."""
+    from cheetah_pose_estimation_b200 import synthetic
+    from oracle import adapters, cameras, cost
+    prob = synthetic.make_problem(S=S, N=N, C=C, seed=seed)
+    rng = np.random.default_rng(seed + 7)
+    tau = rng.uniform(-1.0, 1.0, (S, C)) * tau_scale * np.asarray(prob.h)[:, None]
+    tau[:, 0] = 0.0
+    for s in range(S):
+        pb = adapters.from_synthetic(prob, s)
+        v, a = cost.base_rates(prob.q_true[s], pb.h)
+        pts = cost.delayed_pose(pb, prob.q_true[s], tau[s], v, a)
+        uv = cameras.project(pts, pb.cams[None, :, None, :], pb.cam_model)
+        prob.meas[s, :, :, :, 0, 0:2] = (uv + rng.normal(0, noise, uv.shape)).astype(np.float32)
+        prob.meas[s, :, :, :, 0, 2] = 1.0
+    return prob, tau
+
+
+def test_shutter_delay_gradient_is_exact(gpu):
+    """d cost / d q (incl. the terms through dq_base, ddq_base of frames n, n-1, n-2) and d cost / d tau from K2's
+    per-camera blocks against central differences of the oracle's delayed cost."""
+    import torch
+    from cheetah_pose_estimation_b200 import engine
+    from oracle import adapters, cost
+    S, N, C = 2, 8, 4
+    prob, tau_true = _delayed_problem(S, N, C, 61, 0.5, noise=3.0)
+    batch = prob.to_batch("cuda:0")
+    sv = engine.Solver(gpu, batch)
+    rng = np.random.default_rng(3)
+    q = prob.q_true + rng.normal(0, 0.03, prob.q_true.shape)
+    tau = tau_true + rng.uniform(-0.2, 0.2, tau_true.shape) * np.asarray(prob.h)[:, None]
+    lam_eq = rng.normal(0, 1, (S, N, 26))
+    lam_in = rng.normal(0, 1, (S, N, gpu.n_ineq))
+    batch.lam_eq = torch.as_tensor(lam_eq, device="cuda:0")
+    batch.lam_in = torch.as_tensor(lam_in, device="cuda:0")
+    qd, td = torch.as_tensor(q, device="cuda:0"), torch.as_tensor(tau, device="cuda:0")
+    damp = torch.full((S,), 1e-3, dtype=torch.float64, device="cuda:0")
+    g_tau, curv = sv.assemble_delayed(qd, td, damp, reduced=False)
+    torch.cuda.synchronize()
+    g = sv.g.cpu().numpy()
+    g_tau, curv = g_tau.cpu().numpy(), curv.cpu().numpy()
+    c_gpu = sv.evaluate(qd)["cost"].cpu().numpy()
+    for s in range(S):
+        pb = adapters.from_synthetic(prob, s)
+        pb.mu_eq, pb.mu_in = batch.mu_eq, batch.mu_in
+        f = lambda qq, tt: cost.delayed_cost_terms(pb, qq, tt, lam_eq[s], lam_in[s]).sum()
+        assert np.allclose(c_gpu[s], cost.delayed_cost_terms(pb, q[s], tau[s], lam_eq[s], lam_in[s]), rtol=RTOL, atol=1e-9)
+        for (k, p) in [(0, 0), (0, 2), (1, 1), (2, 0), (3, 2), (5, 1), (7, 0), (7, 2), (4, 5), (2, 30), (6, 4)]:
+            d = np.zeros_like(q[s])
+            eps = 1e-6
+            d[k, p] = eps
+            fd = (f(q[s] + d, tau[s]) - f(q[s] - d, tau[s])) / (2 * eps)
+            assert abs(fd - g[s, k, p]) <= 2e-5 * max(1.0, abs(fd)), (s, k, p, fd, g[s, k, p])
+        for c in range(C):
+            d = np.zeros(C)
+            eps = 2e-7                     # seconds; tau is O(1e-3) and the cost O(1e5): a smaller step drowns in rounding
+            d[c] = eps
+            fd = (f(q[s], tau[s] + d) - f(q[s], tau[s] - d)) / (2 * eps)
+            assert abs(fd - g_tau[s, c]) <= 2e-4 * max(1.0, abs(fd)), (s, c, fd, g_tau[s, c])
+            assert curv[s, c] > 0
+
+
+def test_shutter_delay_estimation_recovers_delays(gpu):
+    """solve_shutter on sequences generated with known per-camera delays: the delays come back, camera 1 stays at 0, and
+    the final cost is below that of the plain solve (tau = 0) of the same data."""
+    import torch
+    from cheetah_pose_estimation_b200 import engine
+    S, N, C = 3, 40, 6
+    prob, tau_true = _delayed_problem(S, N, C, 71, 0.4, noise=1.0)
+    h = np.asarray(prob.h)
+    rng = np.random.default_rng(5)
+    q0 = torch.as_tensor(prob.q_true + rng.normal(0, 0.02, prob.q_true.shape), device="cuda:0")
+    plain = engine.Solver(gpu, prob.to_batch("cuda:0")).solve(q0, max_iter=30, n_outer=3)
+    res = engine.Solver(gpu, prob.to_batch("cuda:0")).solve_shutter(q0, max_iter=30, n_outer=3)
+    torch.cuda.synchronize()
+    tau = res["tau"].cpu().numpy()
+    assert np.all(tau[:, 0] == 0.0) and np.all(np.abs(tau) <= h[:, None])
+    err = np.abs(tau - tau_true) / h[:, None]
+    assert err.max() < 0.1, (err.max(), tau / h[:, None], tau_true / h[:, None])
+    c_plain = plain["cost"][:, 0:2].sum(dim=1).cpu().numpy()
+    c_delay = res["cost"][:, 0:2].sum(dim=1).cpu().numpy()
+    assert np.all(c_delay < c_plain), (c_delay, c_plain)
+    assert float(res["c_eq"].abs().max()) < 1e-3
