@@ -3,9 +3,10 @@
 the `ipopt` call are replaced by the CUDA path (engine.Solver).  `solver_path` is accepted and ignored.
 
 Mirrored beyond the multi-view reconstruction: the monocular data-driven priors (`monocular_constraints=True`,
-SURVEY.md section 8f.1), pairwise pseudo-measurements (`enable_ppm`), hand-labelled detections, and
+SURVEY.md section 8f.1), pairwise pseudo-measurements (`enable_ppm`), hand-labelled detections, shutter-delay
+estimation (`shutter_delay_estimation=True`, section 8f.4: engine.Solver.solve_shutter) and
 `CheetahEstimator.estimate_grf` (section 8f.3, first stage of the kinetic mode).  Not mirrored (out of scope,
-SURVEY.md section 8): `determine_contacts`, `estimate_kinetics` (full 54-row dynamics), shutter-delay estimation.
+SURVEY.md section 8): `determine_contacts`, `estimate_kinetics` (full 54-row dynamics).
 """
 import json
 import os
@@ -65,6 +66,8 @@ class CheetahEstimator:
 
     def solution_details(self, print_infeasible_contraints: bool = False, tolerance: float = 1e-1):
         print("Total cost:", self.get_objective_cost())
+        if getattr(self, "shutter_delay", None) is not None:
+            print("Shutter delay estimation:", [float(t) for t in self.shutter_delay])       # acinoset_opt.py:397-398
         for k, v in (self.costs or {}).items():
             print(f"-- {k}: {v}")
         if print_infeasible_contraints and self.result is not None:
@@ -121,7 +124,13 @@ class CheetahEstimator:
                 sync_offset_arr[offset["cam"]] = offset["frame"]
         out_fpath = os.path.join(out_dir, f"{fname}.pickle")
         misc.save_optimised_cheetah(self.positions, out_fpath, extra_data=dict(**output, start_frame=params.start_frame))
-        misc.save_3d_cheetah_as_2d([self.positions] * scene.n_cams, out_dir, scene.scene_fpath, markers,
+        positions_arr = [self.positions] * scene.n_cams
+        if getattr(self, "shutter_delay", None) is not None:
+            # what camera c sees: pose + dq_base tau_c + ddq_base tau_c^2 (acinoset_opt.py:342-352)
+            assert len(self.shutter_delay) == scene.n_cams
+            positions_arr = [self.positions + self.dq[:, None, 0:3] * t + self.ddq[:, None, 0:3] * (t ** 2)
+                             for t in self.shutter_delay]
+        misc.save_3d_cheetah_as_2d(positions_arr, out_dir, scene.scene_fpath, markers,
                                    misc.project_points if params.kinetic_dataset else misc.project_points_fisheye,
                                    params.start_frame, sync_offset_arr, vid_dir=params.data_dir, out_fname=fname)
         return out_fpath
@@ -155,9 +164,6 @@ def init_trajectory(root_dir: str,
     from . import engine
     if not kinematic_model:
         raise NotImplementedError("kinetic (physics-based) model: out of scope of this path (SURVEY.md section 8f.3)")
-    if shutter_delay_estimation:
-        raise NotImplementedError("shutter-delay estimation is not on this path (SURVEY.md section 8f.4); the delay term "
-                                  "itself is evaluated by cpe_eval_* (cpe_batch.shutter_tau), see DESIGN.md section 10")
     if cheetah_name not in ("jules", "phantom", "shiraz", "arabia"):
         cheetah_name = "acinoset"
     ground_plane_height = 0.0
@@ -249,10 +255,18 @@ def estimate_kinematics(estimator: CheetahEstimator,
                                     cam_model=engine.PINHOLE if params.kinetic_dataset else engine.FISHEYE)
     solver = engine.Solver(estimator.model, batch, priors=priors)
     time0 = time()
-    # the priors pull against the joint equalities: two more multiplier updates keep the violation below the
-    # acceptance threshold of is_solution_acceptable
-    res = solver.solve(torch.as_tensor(q0[None], device=dev), max_iter=max_iter,
-                       n_outer=n_outer + (2 if priors is not None else 0))
+    estimator.shutter_delay = None
+    if scene.cam_idx is None and params.enable_shutter_delay_estimation and priors is None:
+        # per-camera shutter delays next to q (acinoset_misc.py:182-183, 273-286): first the plain solve, then the
+        # joint (q, tau) iterations from its optimum
+        res = solver.solve(torch.as_tensor(q0[None], device=dev), max_iter=max_iter, n_outer=n_outer)
+        res = solver.solve_shutter(res["q"], max_iter=max_iter, n_outer=n_outer)
+        estimator.shutter_delay = res["tau"][0].cpu().numpy()
+    else:
+        # the priors pull against the joint equalities: two more multiplier updates keep the violation below the
+        # acceptance threshold of is_solution_acceptable
+        res = solver.solve(torch.as_tensor(q0[None], device=dev), max_iter=max_iter,
+                           n_outer=n_outer + (2 if priors is not None else 0))
     torch.cuda.synchronize()
     estimator.opt_time_s = time() - time0
     q = res["q"][0].cpu().numpy()

@@ -544,20 +544,21 @@ class Solver:
 def base_rates(bxyz, h, n_frames=None):
     """dq_base, ddq_base [S,N,3] of the q-only formulation: the reference's implicit-Euler collocation
     (collocation.py:58-68: q_n = q_{n-1} + h dq_n, dq_n = dq_{n-1} + h ddq_n) eliminated, i.e. backward differences of
-    the base x, y, z.  The reference leaves dq_1 and ddq_1 (hence ddq_2) free; with them eliminated there is nothing
-    left to define them, so they are continued constantly: dq_0 = dq_1, ddq_0 = ddq_1 = ddq_2 (a deviation from the
-    reference NLP confined to the first two frames, stated in DESIGN.md).  Plain differentiable torch ops on [S,N,3]."""
+    the base x, y, z.  The reference leaves dq and ddq of the first node free (hence ddq of the second); with them
+    eliminated nothing is left to define them, so they take the values that zero their motion cost, as in the saved
+    dq / ddq: ddq_0 = ddq_1 = ddq_2 and dq_0 = dq_1 - h ddq_1 (0-based).  A deviation from the reference
+    NLP confined to the first two frames, stated in DESIGN.md.  Plain differentiable torch ops on [S,N,3]."""
     S, N, _ = bxyz.shape
     hh = h[:, None, None]
     if N < 2:
         z = torch.zeros_like(bxyz)
         return z, z
     v1 = (bxyz[:, 1:] - bxyz[:, :-1]) / hh                                   # frames 1..N-1
-    v = torch.cat([v1[:, :1], v1], dim=1)
     if N < 3:
-        return v, torch.zeros_like(bxyz)
+        return torch.cat([v1[:, :1], v1], dim=1), torch.zeros_like(bxyz)
     a2 = (v1[:, 1:] - v1[:, :-1]) / hh                                       # frames 2..N-1
     a = torch.cat([a2[:, :1], a2[:, :1], a2], dim=1)
+    v = torch.cat([v1[:, :1] - hh * a2[:, :1], v1], dim=1)
     return v, a
 
 

@@ -101,9 +101,9 @@ def delayed_pose(pb: Problem, q, tau=None, dq_base=None, ddq_base=None):
 
 def base_rates(q, h):
     """dq_base, ddq_base [N,3] once the collocation rows (collocation.py:58-68) are eliminated: backward differences
-    of the base x, y, z.  The reference keeps dq_1 and ddq_1 (hence ddq_2) as free variables; in the q-only
-    formulation they are continued constantly, dq_0 = dq_1 and ddq_0 = ddq_1 = ddq_2 (stated deviation, first two
-    frames only)."""
+    of the base x, y, z.  The reference keeps dq and ddq of the first node (hence ddq of the second) as free
+    variables; in the q-only formulation they take the values that zero their motion cost (the same as in
+    the saved dq / ddq): ddq_0 = ddq_1 = ddq_2, dq_0 = dq_1 - h ddq_1 (0-based; stated deviation, first two frames)."""
     b = np.asarray(q, float)[:, 0:3]
     N = b.shape[0]
     v, a = np.zeros_like(b), np.zeros_like(b)
@@ -113,6 +113,7 @@ def base_rates(q, h):
     if N >= 3:
         a[2:] = (v[2:] - v[1:-1]) / h
         a[0] = a[1] = a[2]
+        v[0] = v[1] - h * a[1]
     return v, a
 
 

@@ -99,3 +99,42 @@ def test_monocular_reconstruction_with_data_driven_priors(golden_dir, tmp_path):
     print(f"monocular cam 0: obj {d['obj_cost']:.3f}, costs {est.costs}, MPJPE vs the shipped multi-view trajectory "
           f"{mpjpe:.1f} mm, {d['processing_time_s']:.3f} s")
     assert mpjpe < 250.0
+
+
+def test_shutter_delay_estimation_through_the_mirrored_api(golden_dir, tmp_path):
+    """`init_trajectory(..., shutter_delay_estimation=True)` (acinoset_opt.py:428, acinoset_misc.py:182-183, 273-286) on
+    a real 6-camera clip: delays inside the reference's bounds with camera 1 fixed at 0, an objective no worse than the
+    plain reconstruction of the same data, and per-camera 2-D outputs written from the delayed positions
+    (acinoset_opt.py:342-352)."""
+    import pandas as pd
+    from cheetah_pose_estimation_b200 import acinoset_opt as opt
+    path = "2017_08_29/top/jules/run1_1"
+    g = np.load(os.path.join(golden_dir, "clip_jules_run1_1.npz"))
+    h = 1.0 / float(g["fps"])
+    objs = {}
+    for flag in (False, True):
+        root = os.path.join(str(tmp_path), "delay" if flag else "plain")
+        build_clip_dir(root, path, g)
+        est = opt.init_trajectory(root, path, "jules", kinetic_dataset=False, solver_path="ignored",
+                                  kinematic_model=True, shutter_delay_estimation=flag)
+        assert opt.estimate_kinematics(est, solver_output=True)
+        objs[flag] = (est.get_objective_cost(), est, root)
+    obj_plain, obj_delay = objs[False][0], objs[True][0]
+    est, root = objs[True][1], objs[True][2]
+    tau = est.shutter_delay
+    assert objs[False][1].shutter_delay is None
+    assert tau.shape == (6,) and tau[0] == 0.0 and np.all(np.abs(tau) <= h)
+    print(f"shutter delays / h: {np.round(tau / h, 4)}, objective {obj_delay:.4f} vs plain {obj_plain:.4f}")
+    assert obj_delay <= obj_plain * 1.002
+    out_dir = os.path.join(root, path, "fte_kinematic")
+    d = pickle.load(open(os.path.join(out_dir, "fte.pickle"), "rb"))
+    # camera c's CSV holds the projection of pose + dq tau_c + ddq tau_c^2; camera 1 (tau = 0) that of the pose itself
+    from cheetah_pose_estimation_b200 import acinoset_misc as misc
+    from oracle import cameras
+    for c in (0, 3):
+        df = pd.read_csv(os.path.join(out_dir, f"cam{c + 1}_fte.csv"), header=[0, 1], index_col=0)
+        pts = d["positions"] + d["dq"][:, None, 0:3] * tau[c] + d["ddq"][:, None, 0:3] * tau[c] ** 2
+        uv = cameras.project(pts, g["cams"][c][None, None, :])                     # [N,24,2]
+        got = df.to_numpy().reshape(len(df), 24, 3)[:, :, 0:2]                    # x, y, likelihood (NaN) per bodypart
+        m = np.isfinite(got)
+        assert m.mean() > 0.5 and np.abs(got[m] - uv[m]).max() < 1e-3
