@@ -438,7 +438,7 @@ class Solver:
     # ---- shutter-delay estimation (acinoset_misc.py:182-183, 273-286) ------------------------------------
     def set_delay(self, q, tau):
         """Point the batch at the delay tau[S,C] and at the base velocity / acceleration of q (base_rates)."""
-        v, a = base_rates(q[..., 0:3], self.b.h)
+        v, a = base_rates(q[..., 0:3], self.b.h, self.b.n_frames)
         self.b.shutter_tau, self.b.base_dq, self.b.base_ddq = tau.contiguous(), v.contiguous(), a.contiguous()
 
     def delay_terms(self, q, tau):
@@ -448,7 +448,7 @@ class Solver:
         blk = self.cam_blocks                                                  # [S,N,C,9]
         bx = q[..., 0:3].detach().clone().requires_grad_(True)
         tv = tau.detach().clone().requires_grad_(True)
-        v, a = base_rates(bx, self.b.h)
+        v, a = base_rates(bx, self.b.h, self.b.n_frames)
         d = v[:, :, None, :] * tv[:, None, :, None] + a[:, :, None, :] * (tv * tv)[:, None, :, None]
         (blk[..., 6:9] * d).sum().backward()
         w = (v[:, :, None, :] + 2.0 * tv[:, None, :, None] * a[:, :, None, :]).detach()          # d d / d tau, [S,N,C,3]
@@ -558,7 +558,10 @@ def base_rates(bxyz, h, n_frames=None):
         return torch.cat([v1[:, :1], v1], dim=1), torch.zeros_like(bxyz)
     a2 = (v1[:, 1:] - v1[:, :-1]) / hh                                       # frames 2..N-1
     a = torch.cat([a2[:, :1], a2[:, :1], a2], dim=1)
-    v = torch.cat([v1[:, :1] - hh * a2[:, :1], v1], dim=1)
+    if n_frames is not None:                                                 # ragged batch: sequences shorter than 3 / 2
+        a = a * (n_frames >= 3).to(a.dtype)[:, None, None]                   # frames have no acceleration / velocity
+        v1 = v1 * (n_frames >= 2).to(a.dtype)[:, None, None]
+    v = torch.cat([v1[:, :1] - hh * a[:, 1:2], v1], dim=1)
     return v, a
 
 

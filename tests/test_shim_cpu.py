@@ -164,3 +164,23 @@ def test_hand_labelled_packing(tmp_path):
                 else:
                     assert meas[n, c, l, 0, 0] == np.float32(x) and meas[n, c, l, 0, 1] == np.float32(y)
                     assert meas[n, c, l, 0, 2] == 1.0
+
+
+def test_base_rates_match_the_oracle_and_the_collocation_rows():
+    """engine.base_rates (host-side torch plumbing of the shutter-delay driver) against the oracle's restatement, on a
+    ragged batch, and against the implicit-Euler rows it eliminates (collocation.py:58-68)."""
+    import torch
+    from cheetah_pose_estimation_b200 import engine
+    from oracle import cost
+    rng = np.random.default_rng(4)
+    q = rng.normal(size=(4, 9, 54))
+    h = np.array([1 / 90, 1 / 120, 1 / 200, 1 / 90])
+    nf = np.array([9, 3, 2, 1], np.int32)
+    v, a = engine.base_rates(torch.as_tensor(q[..., 0:3]), torch.as_tensor(h), torch.as_tensor(nf))
+    for s in range(4):
+        vo, ao = cost.base_rates(q[s, :nf[s]], h[s])
+        assert np.array_equal(v[s, :nf[s]].numpy(), vo) and np.array_equal(a[s, :nf[s]].numpy(), ao)
+    b, vv, aa = q[0, :, 0:3], v[0].numpy(), a[0].numpy()
+    assert np.abs(b[1:] - b[:-1] - h[0] * vv[1:]).max() < 1e-14          # q_n = q_{n-1} + h dq_n
+    assert np.abs(vv[1:] - vv[:-1] - h[0] * aa[1:]).max() < 1e-10        # dq_n = dq_{n-1} + h ddq_n, incl. the first node
+    assert np.array_equal(aa[0], aa[1]) and np.array_equal(aa[1], aa[2])
