@@ -51,6 +51,7 @@ def parse_args():
     ap.add_argument("--lm-split", type=int, default=1, help="sub-batches of the LM leg solved on separate streams")
     ap.add_argument("--mono-seqs", type=int, default=60, help="monocular hypotheses of the config-3 leg (0 = skip)")
     ap.add_argument("--grf-seqs", type=int, default=444, help="sequences of the GRF-estimate leg (0 = skip)")
+    ap.add_argument("--shutter-seqs", type=int, default=148, help="sequences of the shutter-delay leg (0 = skip)")
     ap.add_argument("--cpu-seqs", type=int, default=64, help="sequences of the cpu_baseline sample (0 = skip)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-f32", action="store_true", help="skip the FP32-flavour leg")
@@ -396,6 +397,48 @@ def monocular_leg(a, r):
             "priors": "GMM(5) pose prior + AR(4) motion prior fitted on the synthetic trajectories (CPU, untimed)"}
 
 
+def shutter_leg(a, r):
+    """Shutter-delay estimation: S sequences x 100 frames x 6 cameras whose detections follow the delayed
+    measurement model with known per-camera delays (projections taken from K1 itself at the true trajectory, 1 px noise);
+    `solve_shutter` from a perturbed trajectory and tau = 0."""
+    import torch
+    from cheetah_pose_estimation_b200 import engine, synthetic
+    S = a.shutter_seqs
+    if S <= 0:
+        return None
+    N, C, dev = 100, 6, r["dev"]
+    batch, q_true, _ = synthetic.make_device_problem(S, N, C, seed=a.seed + 33 + 1000 * r["rank"], device=dev)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(a.seed + 34)
+    h = batch.h
+    tau_true = (torch.rand(S, C, generator=gen, device=dev, dtype=torch.float64) * 2 - 1) * 0.4 * h[:, None]
+    tau_true[:, 0] = 0.0
+    batch.meas[..., 0:2] = 0.0                               # residual against zero detections = the delayed projection
+    gen_sv = engine.Solver(r["model"], batch, with_solver=False)
+    gen_sv.set_delay(q_true, tau_true)
+    uv = gen_sv.evaluate(q_true.contiguous(), resid=True)["resid"]
+    noise = torch.randn(uv.shape, generator=gen, device=dev, dtype=torch.float64)
+    batch.meas[..., 0:2] = (uv + noise).to(batch.meas.dtype)
+    batch.shutter_tau = batch.base_dq = batch.base_ddq = None
+    q0 = (q_true + 0.02 * torch.randn(q_true.shape, generator=gen, device=dev, dtype=torch.float64)).contiguous()
+    sv = engine.Solver(r["model"], batch)
+    sv.solve_shutter(q0, max_iter=2, n_outer=1)
+    l0 = sv.launches
+    r["barrier"]()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    res = sv.solve_shutter(q0, max_iter=a.lm_iters, n_outer=3)
+    e1.record()
+    r["barrier"]()
+    ms = e0.elapsed_time(e1)
+    err = (res["tau"] - tau_true).abs() / h[:, None]
+    return {"sequences": S, "frames": N, "cams": C, "sequences_per_s": S / (ms * 1e-3), "ms": ms,
+            "lockstep_iterations": res["lockstep_iterations"], "launches": sv.launches - l0,
+            "delay_error_frames_median": float(err[:, 1:].median()), "delay_error_frames_max": float(err.max()),
+            "true_delay_frames_max": 0.4, "final_cost_mean": float(res["cost"][:, :2].sum(dim=1).mean()),
+            "max_abs_joint_violation": float(res["c_eq"].abs().max()), "failed_pivots": int(res["status"].sum())}
+
+
 def grf_leg(a, r):
     """Per-frame GRF estimate (cpe_eom_affine_f64 + cpe_grf_solve_f64) on the LM leg's trajectories: frames/s."""
     import numpy as np
@@ -488,6 +531,7 @@ def main():
         lm["sequences_per_s"] = lm["sequences"] / (lm["ms"] * 1e-3)
     mono = monocular_leg(a, r) if world == 1 else None
     grf = grf_leg(a, r) if world == 1 else None
+    shutter = shutter_leg(a, r) if world == 1 else None
     if rank == 0:
         fv_rank = a.seqs * a.frames * a.cams
         fv_total = fv_rank * world
@@ -539,6 +583,8 @@ def main():
             line["monocular"] = mono
         if grf is not None:
             line["grf"] = grf
+        if shutter is not None:
+            line["shutter"] = shutter
         if world == 1:
             line["cpu_baseline"] = cpu_baseline_leg(a)
         _emit(line)

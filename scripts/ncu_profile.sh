@@ -2,7 +2,7 @@
 # usage (on the GPU box): bash scripts/ncu_profile.sh <tag>
 set -x
 TAG=${1:-rX}
-CMD="python bench.py --no-f32 --mono-seqs 60 --grf-seqs 64 --seqs 64 --wave 32 --lm-seqs 16 --lm-iters 4 --cpu-seqs 0 --steps 2 --warmup 1 --no-e2e"
+CMD="python bench.py --no-f32 --mono-seqs 60 --grf-seqs 64 --shutter-seqs 0 --seqs 64 --wave 32 --lm-seqs 16 --lm-iters 4 --cpu-seqs 0 --steps 2 --warmup 1 --no-e2e"
 K="eval_kernel|assemble_kernel|band_|step_apply|reduce_|step_accept|update_multipliers|prior_kernel|eom_|grf_"
 $CMD > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"$K" -c 1500 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/ncu1.log 2>&1
