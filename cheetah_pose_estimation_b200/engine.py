@@ -393,8 +393,10 @@ class Solver:
         prior_try = torch.zeros(S, 2, dtype=torch.float64, device=dev) if self.priors is not None else None
         damp = self.state[1]
         total_inner = 0
+        ftols = tuple(ftol) if isinstance(ftol, (tuple, list)) else (ftol,)
         for outer in range(n_outer):
             b.mu_eq = b.mu_in = float(mu_schedule[min(outer, len(mu_schedule) - 1)])
+            ftol = float(ftols[min(outer, len(ftols) - 1)])      # inexact inner solves while the multipliers are rough
             self.evaluate(q)
             self.state[0].copy_(self.cost.sum(dim=1))
             if self.priors is not None:

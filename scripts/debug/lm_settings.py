@@ -19,6 +19,11 @@ cfgs = {
     "mu1e5,1e6": dict(max_iter=20, n_outer=2, mu_schedule=(1e5, 1e6)),
     "mu1e6x2": dict(max_iter=20, n_outer=2, mu_schedule=(1e6, 1e6)),
     "mu1e5,1e6,1e6": dict(max_iter=20, n_outer=3, mu_schedule=(1e5, 1e6, 1e6)),
+    "ftol 1e-3,1e-5,1e-6": dict(max_iter=20, n_outer=3, ftol=(1e-3, 1e-5, 1e-6)),
+    "ftol 1e-4,1e-5,1e-6": dict(max_iter=20, n_outer=3, ftol=(1e-4, 1e-5, 1e-6)),
+    "ftol 1e-2,1e-4,1e-6": dict(max_iter=20, n_outer=3, ftol=(1e-2, 1e-4, 1e-6)),
+    "ftol 1e-4,1e-4,1e-6": dict(max_iter=20, n_outer=3, ftol=(1e-4, 1e-4, 1e-6)),
+    "it 12,20,20": dict(max_iter=12, n_outer=3),
 }
 sv = engine.Solver(model, batch)
 sv.solve(q0, max_iter=2, n_outer=1)
@@ -30,6 +35,6 @@ for name, kw in cfgs.items():
     dt = time.time() - t0
     cost = r["cost"][:, :2].sum(dim=1)
     err = (r["q"][:, :, :3] - q_true[:, :, :3]).norm(dim=-1).mean()
-    print(f"{name:16s} {dt*1e3:8.1f} ms  lockstep {r['lockstep_iterations']:3d}  mean it {r['counters'][:,0].double().mean():5.1f}"
+    print(f"{name:20s} {dt*1e3:8.1f} ms  lockstep {r['lockstep_iterations']:3d}  mean it {r['counters'][:,0].double().mean():5.1f}"
           f"  cost mean {cost.mean():.4f} max {cost.max():.2f}  c_eq {r['c_eq'].abs().max():.2e}  v_in {r['v_in'].abs().max():.2e}"
           f"  base err {err*1e3:.3f} mm  fail {int(r['status'].sum())}")
