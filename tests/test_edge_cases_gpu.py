@@ -150,3 +150,28 @@ def test_full_sweep_size_wave_split_and_checksum(gpu):
     assert torch.equal(whole[:32, 2:], whole[32:64, 2:]) and torch.equal(whole[:32, 1], whole[32:64, 1])
     w32 = sv.evaluate(q, f32=True)["cost"]
     assert float(((w32[:, 0] - whole[:, 0]).abs() / whole[:, 0].abs()).max()) < 1e-6
+
+
+def test_shutter_delay_estimation_on_ragged_and_tiny_sequences(gpu):
+    """solve_shutter next to sequences that are too short to carry a velocity or an acceleration (0, 1, 2 frames) and a
+    ragged tail: everything stays finite, the delays stay inside +-1/fps with camera 1 at 0, frames beyond n_frames are
+    left untouched, and the full-length sequence still lowers its cost against tau = 0."""
+    import torch
+    from cheetah_pose_estimation_b200 import engine
+    prob, q, qd = _problem(5, 24, 6, 47)
+    nf = np.array([0, 1, 2, 17, 24], np.int32)
+    batch = prob.to_batch("cuda:0")
+    batch.n_frames = torch.as_tensor(nf, device="cuda:0")
+    sv = engine.Solver(gpu, batch)
+    c0 = sv.evaluate(qd)["cost"].sum(dim=1).clone()
+    res = sv.solve_shutter(qd, max_iter=15, n_outer=2)
+    torch.cuda.synchronize()
+    tau, qs = res["tau"].cpu().numpy(), res["q"].cpu().numpy()
+    h = np.asarray(prob.h)
+    assert np.isfinite(tau).all() and np.isfinite(qs).all() and np.isfinite(res["cost"].cpu().numpy()).all()
+    assert np.all(tau[:, 0] == 0.0) and np.all(np.abs(tau) <= h[:, None])
+    assert not np.any(tau[0]) and not np.any(tau[1])          # no frames / one frame: no rates, nothing to estimate from
+    for s in range(5):
+        assert np.array_equal(qs[s, nf[s]:], q[s, nf[s]:])
+    assert int(res["status"].sum()) == 0
+    assert float(res["cost"][4, 0:2].sum()) < float(c0[4])
