@@ -87,6 +87,8 @@ EXPORTS = {
     "cpe_eom_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p, c_f64p, c_f64p, c_f64p, C.c_void_p]),
     "cpe_eom_affine_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p, c_f64p, c_f64p, c_f64p, C.c_void_p]),
     "cpe_grf_solve_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, c_i32p, C.c_int32, c_f64p, c_f64p, C.c_void_p]),
+    "cpe_base_rates_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p, C.c_void_p]),
+    "cpe_shutter_terms_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p, c_f64p, C.c_void_p]),
     "cpe_update_multipliers_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p,
                                              c_f64p, C.c_void_p]),
     "cpe_eval_host_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpeBatch), C.c_void_p, C.c_void_p, c_f64p,

@@ -439,26 +439,33 @@ class Solver:
 
     # ---- shutter-delay estimation (acinoset_misc.py:182-183, 273-286) ------------------------------------
     def set_delay(self, q, tau):
-        """Point the batch at the delay tau[S,C] and at the base velocity / acceleration of q (base_rates)."""
-        v, a = base_rates(q[..., 0:3], self.b.h, self.b.n_frames)
-        self.b.shutter_tau, self.b.base_dq, self.b.base_ddq = tau.contiguous(), v.contiguous(), a.contiguous()
+        """Point the batch at the delay tau[S,C] and at the base velocity / acceleration of q (cpe_base_rates_f64)."""
+        b = self.b
+        if not hasattr(self, "_dqb"):
+            self._dqb = torch.zeros(b.S, b.N, 3, dtype=torch.float64, device=q.device)
+            self._ddqb = torch.zeros_like(self._dqb)
+        b.shutter_tau, b.base_dq, b.base_ddq = tau.contiguous(), self._dqb, self._ddqb
+        bs = b.struct()
+        _lib.check(self.lib.cpe_base_rates_f64(C.byref(bs), _ptr(q), _ptr(self._dqb), _ptr(self._ddqb), _stream()),
+                   "cpe_base_rates_f64")
+        self.launches += 1
 
     def delay_terms(self, q, tau):
         """From the per-camera blocks of the last `assemble` at (q, tau): the part of d cost / d q that goes through
         dq_base and ddq_base (g_extra[S,N,3], on the base x, y, z of frames n, n-1, n-2), d cost / d tau [S,C], and the
         Gauss-Newton curvature of tau [S,C] (cameras do not share residuals, so it is diagonal)."""
-        blk = self.cam_blocks                                                  # [S,N,C,9]
-        bx = q[..., 0:3].detach().clone().requires_grad_(True)
-        tv = tau.detach().clone().requires_grad_(True)
-        v, a = base_rates(bx, self.b.h, self.b.n_frames)
-        d = v[:, :, None, :] * tv[:, None, :, None] + a[:, :, None, :] * (tv * tv)[:, None, :, None]
-        (blk[..., 6:9] * d).sum().backward()
-        w = (v[:, :, None, :] + 2.0 * tv[:, None, :, None] * a[:, :, None, :]).detach()          # d d / d tau, [S,N,C,3]
-        A = blk[..., 0:6]
-        curv = (A[..., 0] * w[..., 0] ** 2 + A[..., 3] * w[..., 1] ** 2 + A[..., 5] * w[..., 2] ** 2
-                + 2.0 * (A[..., 1] * w[..., 0] * w[..., 1] + A[..., 2] * w[..., 0] * w[..., 2]
-                         + A[..., 4] * w[..., 1] * w[..., 2])).sum(dim=1)
-        return bx.grad, tv.grad, curv
+        b = self.b
+        assert b.shutter_tau is not None and q.is_contiguous()
+        if not hasattr(self, "_g_extra"):
+            self._g_extra = torch.zeros(b.S, b.N, 3, dtype=torch.float64, device=q.device)
+            self._g_tau = torch.zeros(b.S, b.C, dtype=torch.float64, device=q.device)
+            self._curv_tau = torch.zeros_like(self._g_tau)
+        bs = b.struct()
+        _lib.check(self.lib.cpe_shutter_terms_f64(C.byref(bs), _ptr(self.cam_blocks), _ptr(self._g_extra),
+                                                  _ptr(self._g_tau), _ptr(self._curv_tau), _stream()),
+                   "cpe_shutter_terms_f64")
+        self.launches += 2
+        return self._g_extra, self._g_tau, self._curv_tau
 
     def assemble_delayed(self, q, tau, damp, reduced=True):
         """`assemble` at (q, tau) with the exact gradient: K2 gives d cost / d q_n at fixed dq, ddq; the terms through

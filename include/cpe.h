@@ -300,6 +300,17 @@ int cpe_eom_affine_f64(const cpe_batch *batch, const double *q, const double *dq
 int cpe_grf_solve_f64(const cpe_batch *batch, const double *a, const double *Bm, const int32_t *contact, int32_t iters,
                       double *grf, double *resid, void *stream);
 
+/* Shutter-delay estimation (acinoset_misc.py:182-183, 273-286): the pieces that are not per-residual work.
+ * cpe_base_rates_f64: dq_base, ddq_base [S,N,3] of q in the q-only formulation -- backward differences of the base
+ * x, y, z (collocation.py:58-68 eliminated), first-node values as in the saved dq / ddq (ddq_0 = ddq_1 = ddq_2,
+ * dq_0 = dq_1 - h ddq_1); zero for frames beyond n_frames and for sequences too short to have them.
+ * cpe_shutter_terms_f64: from cpe_assemble_out.cam_blocks of an assembly at (q, tau) -- batch carries shutter_tau,
+ * base_dq, base_ddq -- g_extra[S,N,3] = the part of d cost / d (base x, y, z) that goes through dq_base and ddq_base
+ * (frame n feeds frames n, n-1, n-2), g_tau[S,C] = d cost / d tau_c, curv_tau[S,C] = its Gauss-Newton curvature. */
+int cpe_base_rates_f64(const cpe_batch *batch, const double *q, double *dq_base, double *ddq_base, void *stream);
+int cpe_shutter_terms_f64(const cpe_batch *batch, const double *cam_blocks, double *g_extra, double *g_tau,
+                          double *curv_tau, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
