@@ -476,9 +476,12 @@ def test_shutter_delay_gradient_is_exact(gpu):
     import torch
     from cheetah_pose_estimation_b200 import engine
     from oracle import adapters, cost
-    S, N, C = 2, 8, 4
+    S, N, C = 4, 8, 4
     prob, tau_true = _delayed_problem(S, N, C, 61, 0.5, noise=3.0)
+    nf = np.array([8, 8, 3, 2], np.int32)        # the first-node rules differ for 3- and 2-frame sequences
+    prob.n_frames = nf
     batch = prob.to_batch("cuda:0")
+    batch.n_frames = torch.as_tensor(nf, device="cuda:0")
     sv = engine.Solver(gpu, batch)
     rng = np.random.default_rng(3)
     q = prob.q_true + rng.normal(0, 0.03, prob.q_true.shape)
@@ -497,19 +500,23 @@ def test_shutter_delay_gradient_is_exact(gpu):
     for s in range(S):
         pb = adapters.from_synthetic(prob, s)
         pb.mu_eq, pb.mu_in = batch.mu_eq, batch.mu_in
-        f = lambda qq, tt: cost.delayed_cost_terms(pb, qq, tt, lam_eq[s], lam_in[s]).sum()
-        assert np.allclose(c_gpu[s], cost.delayed_cost_terms(pb, q[s], tau[s], lam_eq[s], lam_in[s]), rtol=RTOL, atol=1e-9)
-        for (k, p) in [(0, 0), (0, 2), (1, 1), (2, 0), (3, 2), (5, 1), (7, 0), (7, 2), (4, 5), (2, 30), (6, 4)]:
-            d = np.zeros_like(q[s])
+        n = int(nf[s])
+        qs, le, li = q[s, :n], lam_eq[s, :n], lam_in[s, :n]
+        f = lambda qq, tt: cost.delayed_cost_terms(pb, qq, tt, le, li).sum()
+        assert np.allclose(c_gpu[s], cost.delayed_cost_terms(pb, qs, tau[s], le, li), rtol=RTOL, atol=1e-9)
+        for (k, p) in [(0, 0), (0, 2), (1, 1), (2, 0), (3, 2), (5, 1), (7, 0), (7, 2), (4, 5), (2, 30), (6, 4), (1, 0)]:
+            if k >= n:
+                continue
+            d = np.zeros_like(qs)
             eps = 1e-6
             d[k, p] = eps
-            fd = (f(q[s] + d, tau[s]) - f(q[s] - d, tau[s])) / (2 * eps)
+            fd = (f(qs + d, tau[s]) - f(qs - d, tau[s])) / (2 * eps)
             assert abs(fd - g[s, k, p]) <= 2e-5 * max(1.0, abs(fd)), (s, k, p, fd, g[s, k, p])
         for c in range(C):
             d = np.zeros(C)
             eps = 2e-7                     # seconds; tau is O(1e-3) and the cost O(1e5): a smaller step drowns in rounding
             d[c] = eps
-            fd = (f(q[s], tau[s] + d) - f(q[s], tau[s] - d)) / (2 * eps)
+            fd = (f(qs, tau[s] + d) - f(qs, tau[s] - d)) / (2 * eps)
             assert abs(fd - g_tau[s, c]) <= 2e-4 * max(1.0, abs(fd)), (s, c, fd, g_tau[s, c])
             assert curv[s, c] > 0
 
