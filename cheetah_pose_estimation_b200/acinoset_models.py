@@ -21,7 +21,7 @@ def read_dataset(fname):
     if ext == ".h5":
         try:
             return pd.read_hdf(fname)
-        except Exception:                                   # PyTables absent: the shipped CSV holds the same table
+        except (ImportError, FileNotFoundError):                                 # PyTables absent: the shipped CSV holds the same table
             return pd.read_csv(base + ".csv", index_col=0)
     return pd.read_csv(fname, index_col=0)
 

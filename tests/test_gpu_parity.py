@@ -336,7 +336,6 @@ def test_skipping_converged_sequences_changes_nothing(gpu):
     torch.cuda.synchronize()
     for k in ("q", "cost", "counters"):
         assert torch.equal(res[0][k], res[1][k]), k
-    assert int(res[0]["counters"][:, 0].min()) < int(res[0]["counters"][:, 0].max()) or True
 
 
 def test_solve_split_is_bit_identical(gpu):
