@@ -36,6 +36,7 @@ class CpeBatch(C.Structure):
         ("n_frames", c_i32p), ("h", c_f64p), ("meas", C.c_void_p), ("cams", c_f64p), ("chain_vec", c_f64p),
         ("lam_eq", c_f64p), ("lam_in", c_f64p), ("active", c_i32p),
         ("shutter_tau", c_f64p), ("base_dq", c_f64p), ("base_ddq", c_f64p),
+        ("n_cams", c_i32p),
     ]
 
 

@@ -88,23 +88,41 @@ def find_scene_file(dir_path, scene_fname=None, verbose=True):
     raise FileNotFoundError(ENOENT, os.strerror(ENOENT), os.path.join("extrinsic_calib", scene_fname))
 
 
-def _read_dlc_file(path):
-    """One camera's DLC predictions as float array [frames, 75] (x, y, likelihood per body part).
-    `.h5` is the reference's format (pandas HDF, needs PyTables); `.csv` is DeepLabCut's own CSV twin of the same
-    table (3 header rows) and `.npy` a raw dump -- both accepted because PyTables may be absent."""
+class DlcData(list):
+    """Per-camera DLC tables, `self[c]` = float array [rows, 75] (or [rows, 50] hand-labelled) addressed by ROW POSITION
+    as the reference's `base_data[cam] = list(df.to_numpy())` (acinoset_misc.py:207); `first_frame[c]` = frame number
+    of row 0 (the DataFrame index the reference's `load_dlc_points_as_df` works with, :1545-1572)."""
+
+    def __init__(self, arrays=(), first_frame=None):
+        super().__init__(arrays)
+        self.first_frame = list(first_frame) if first_frame is not None else [0] * len(self)
+
+
+def _hand_label_frame(ix):
+    """Frame number of a hand-labelled row: characters 3..5 of the image name, `img053.png` -> 53
+    (`int(dlc_df.index[0][-1][3:6])`, acinoset_misc.py:1550-1551); the index entry is a tuple of path parts (h5) or
+    one path string (DeepLabCut's CSV twin)."""
+    name = ix[-1] if isinstance(ix, tuple) else os.path.basename(str(ix).replace("\\", "/"))
+    return int(name[3:6])
+
+
+def _read_dlc_file(path, hand_labeled=False):
+    """One camera's DLC predictions as (float array [rows, 75], frame number of row 0).  `.h5` is the reference's
+    format (pandas HDF, needs PyTables); `.csv` is DeepLabCut's own CSV twin of the same table (3 header rows) and
+    `.npy` a raw dump starting at frame 0 -- both accepted because PyTables may be absent.  Hand-labelled tables hold
+    (x, y) pairs per part, [rows, 50], and name their rows by image file."""
     ext = os.path.splitext(path)[1]
     if ext == ".npy":
-        return np.load(path).astype(np.float64)
+        return np.load(path).astype(np.float64), 0
     import pandas as pd
     if ext == ".csv":
         df = pd.read_csv(path, header=[0, 1, 2], index_col=0)
     else:
         df = pd.read_hdf(path)          # raises ImportError without PyTables -- no silent substitute
-    first = int(df.index[0]) if len(df.index) else 0
-    arr = df.to_numpy(dtype=np.float64)
-    if first > 0:                       # rows are addressed by frame number (acinoset_misc.py:224)
-        arr = np.concatenate([np.full((first, arr.shape[1]), np.nan), arr])
-    return arr
+    if not len(df.index):
+        return df.to_numpy(dtype=np.float64), 0
+    first = _hand_label_frame(df.index[0]) if hand_labeled else int(df.index[0])
+    return df.to_numpy(dtype=np.float64), first
 
 
 def dlc_files(dlc_dir):
@@ -116,11 +134,12 @@ def dlc_files(dlc_dir):
     return []
 
 
-def load_dlc_arrays(dlc_dir, n_cams=None):
+def load_dlc_arrays(dlc_dir, n_cams=None, hand_labeled=False):
     files = dlc_files(dlc_dir)
     if n_cams is not None:
         assert n_cams == len(files), f"# of dlc files != # of cams in {n_cams}_cam_scene_sba.json"
-    return [_read_dlc_file(p) for p in files]
+    tabs = [_read_dlc_file(p, hand_labeled) for p in files]
+    return DlcData([t[0] for t in tabs], [t[1] for t in tabs])
 
 
 PW_SUFFIX = "DLC_resnet152_CheetahOct14shuffle4_650000.pickle"      # acinoset_misc.py:203-205
@@ -141,9 +160,9 @@ def load_pairwise(dlc_dir, n_cams=None):
 
 
 def pack_measurements(params: TrajectoryParams, scene: Scene, base_data, pw_data=None):
-    """meas[N,C,24,W,4] float32 = (u, v, gate, 0) in marker order, C = all cameras or the single monocular one.
-    Row of camera c for frame n: (n-1) + start_frame - sync_offset[c]  (acinoset_misc.py:224, 246); gate =
-    likelihood > dlc_thresh (strict, :231).  NaN detections get gate 0 (documented divergence).
+    """meas[N,C,24,W,4] float32 (float64 for the kinetic dataset) = (u, v, gate, 0) in marker order, C = all cameras or the single monocular one.
+    Row of camera c for frame n: (n-1) + start_frame - sync_offset[c]  (acinoset_misc.py:224, 246), a ROW POSITION of
+    the table as in the reference (not a frame label); gate = likelihood > dlc_thresh (strict, :231).  NaN detections get gate 0 (documented divergence).
     W = 1, or 3 with `params.enable_ppms`: hypotheses w = 2, 3 are pairwise pseudo-measurements
     `pose[base] + pws[0, base, dlc_index[marker]]` with `base = pairwise_graph[marker][w-2]`, gated by the
     likelihood of the base part (acinoset_misc.py:225-228, 249-254)."""
@@ -155,7 +174,8 @@ def pack_measurements(params: TrajectoryParams, scene: Scene, base_data, pw_data
             sync[off["cam"]] = off["frame"]
     cams = list(range(scene.n_cams)) if scene.cam_idx is None else [scene.cam_idx]
     idx = np.array(sk.DLC_INDEX)
-    meas = np.zeros((N, len(cams), 24, W, 4), np.float32)
+    # AcinoSet detections are float32 DLC output; the kinetic dataset's 2-D points are not: keep those in double
+    meas = np.zeros((N, len(cams), 24, W, 4), np.float64 if params.kinetic_dataset else np.float32)
     for ci, c in enumerate(cams):
         if params.hand_labeled_data:
             # hand labels: (x, y) pairs per part, rows NOT shifted by the sync offset, likelihood 1
@@ -218,15 +238,22 @@ def triangulate_points_single_img(img_pts, dist_to_plane, K, D, R, t):
 
 
 def create_trajectory_estimate(base_length, params: TrajectoryParams, scene: Scene, kinetic_dataset: bool,
-                               base_data=None):
+                               base_data=None, robust=True):
     """Initial base track and heading (acinoset_misc.py:381-456): pairwise triangulation of the `spine` detections
     above the likelihood threshold, a smoothing spline per axis over absolute frame numbers, yaw from finite
     differences (+ pi: "assumes running in +x").  Returns x_est, y_est, z_est, psi_est indexed by absolute frame.
-    `base_length` replaces `robot["base"].length`."""
+    `base_length` replaces `robot["base"].length`.  Rows are addressed by FRAME NUMBER here (row position +
+    `base_data.first_frame[c]`), as the reference's DataFrame path does.  Hand-labelled tables (:425-439): (x, y) pairs
+    per part, no likelihood filter, unlabelled frames stay NaN and enter the spline with weight 0.
+    `robust=True` (default) adds two guards that do nothing on clean input and are the only deviations from the
+    reference's initial guess: one re-fit of the splines without gross triangulation outliers, and unwrapping of the
+    heading across atan2's branch cut; `robust=False` is the reference's literal procedure."""
     from scipy.interpolate import UnivariateSpline
+    hand = params.hand_labeled_data
     if base_data is None:
-        dlc_dir = os.path.join(params.data_dir, "dlc" if not params.hand_labeled_data else "dlc_hand_labeled")
-        base_data = load_dlc_arrays(dlc_dir)
+        dlc_dir = os.path.join(params.data_dir, "dlc" if not hand else "dlc_hand_labeled")
+        base_data = load_dlc_arrays(dlc_dir, hand_labeled=hand)
+    first = getattr(base_data, "first_frame", [0] * len(base_data))
     spine = sk.DLC_INDEX[sk.MARKERS.index("spine")]
     sync = {}
     if params.sync_offset is not None:
@@ -235,11 +262,13 @@ def create_trajectory_estimate(base_length, params: TrajectoryParams, scene: Sce
     per_cam = {}
     for c, d in enumerate(base_data):
         d = np.asarray(d)
-        x, y, lik = d[:, 3 * spine], d[:, 3 * spine + 1], d[:, 3 * spine + 2]
-        ok = np.isfinite(x) & np.isfinite(y)
-        if not params.hand_labeled_data:
-            ok &= lik > params.dlc_thresh
-        frames = np.nonzero(ok)[0] + sync.get(c, 0)
+        if hand:
+            x, y = d[:, 2 * spine], d[:, 2 * spine + 1]
+            ok = np.ones(len(x), bool)                       # NaN labels are kept (weight 0 in the spline)
+        else:
+            x, y, lik = d[:, 3 * spine], d[:, 3 * spine + 1], d[:, 3 * spine + 2]
+            ok = np.isfinite(x) & np.isfinite(y) & (lik > params.dlc_thresh)
+        frames = np.nonzero(ok)[0] + first[c] + sync.get(c, 0)
         per_cam[c] = (frames, np.stack([x[ok], y[ok]], 1).astype(np.float32))
     k = 1 if kinetic_dataset else 3
     if scene.cam_idx is None:
@@ -261,21 +290,54 @@ def create_trajectory_estimate(base_length, params: TrajectoryParams, scene: Sce
             for f, p in zip(common, p3):
                 acc.setdefault(int(f), []).append(p)
         frames = np.array(sorted(acc))
-        spine_pts = np.array([[f, *np.mean(acc[f], axis=0)] for f in frames], dtype=np.float64)
+        with np.errstate(invalid="ignore"):
+            import warnings
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore", RuntimeWarning)           # all-NaN frames of hand labels
+                spine_pts = np.array([[f, *np.nanmean(np.asarray(acc[f], dtype=np.float64), axis=0)] for f in frames],
+                                     dtype=np.float64)
     else:
         c = scene.cam_idx
         fa, pa = per_cam[c]
         xw = triangulate_points_single_img(pa, 3, scene.k_arr[c], scene.d_arr[c], scene.r_arr[c], scene.t_arr[c]).T
         spine_pts = np.c_[fa.astype(np.float64), xw]
     spine_pts[:, 1] = spine_pts[:, 1] + float(base_length) / 2.0
-    frame_est = np.arange(params.end_frame)
-    x_est = np.array(UnivariateSpline(spine_pts[:, 0], spine_pts[:, 1], k=k)(frame_est))
-    y_est = np.array(UnivariateSpline(spine_pts[:, 0], spine_pts[:, 2], k=k)(frame_est))
-    z_est = np.array(UnivariateSpline(spine_pts[:, 0], spine_pts[:, 3], k=k)(frame_est))
+    if hand:
+        # one (possibly NaN) sample per frame 0..max, NaN samples weighted 0 (acinoset_misc.py:425-439); frames before
+        # the first label are absent in the reference's table -- here they are NaN samples of weight 0 as well
+        num_frames = int(spine_pts[:, 0].max()) + 1
+        frame_est = np.arange(num_frames)
+        vals = np.full((num_frames, 3), np.nan)
+        vals[spine_pts[:, 0].astype(int)] = spine_pts[:, 1:4]
+        w = np.isnan(vals).any(axis=1)
+        vals[w] = 0.0
+        x_est, y_est, z_est = (np.array(UnivariateSpline(frame_est, vals[:, i], w=(~w).astype(float), k=k)(frame_est))
+                               for i in range(3))
+    else:
+        frame_est = np.arange(params.end_frame)
+        keep = np.ones(len(spine_pts), bool)
+        for _ in range(2 if robust else 1):
+            fits = [UnivariateSpline(spine_pts[keep, 0], spine_pts[keep, i], k=k) for i in (1, 2, 3)]
+            if not robust:
+                break
+            # one re-fit without gross outliers of the triangulation (a wrong spine detection that passed the likelihood
+            # gate): points further than max(5 MAD, 0.25 m) from the first fit.  Nothing is dropped on clean tracks, where
+            # this is exactly the reference's single fit.
+            dev = np.sqrt(sum((f(spine_pts[:, 0]) - spine_pts[:, i]) ** 2 for f, i in zip(fits, (1, 2, 3))))
+            thr = max(5.0 * 1.4826 * float(np.median(dev)), 0.25)
+            new_keep = dev <= thr
+            if new_keep.all() or new_keep.sum() <= k + 1:
+                break
+            keep = new_keep
+        x_est, y_est, z_est = (np.array(f(frame_est)) for f in fits)
     dx_est = np.diff(x_est) * scene.fps
     dy_est = np.diff(y_est) * scene.fps
     psi_est = np.arctan2(dy_est, dx_est)
     psi_est = np.pi + np.append(psi_est, [psi_est[-1]])
+    if robust:
+        # atan2's branch cut: a heading that crosses +-pi would jump by 2 pi between frames, which the motion model
+        # penalises although it is the same orientation; identical to the reference whenever there is no crossing
+        psi_est = np.unwrap(psi_est)
     return x_est, y_est, z_est, psi_est
 
 
@@ -402,3 +464,29 @@ def traj_error(X, Y, centered=False):
         Y = Y - np.expand_dims(np.mean(Y, axis=1), axis=1)
     distances = np.sqrt(np.sum((X - Y) ** 2, axis=2))
     return 1000.0 * np.mean(distances, axis=0)
+
+
+def compare_traj_error(params: TrajectoryParams, scene: Scene, include_kinetic=False, kinetic_out_fname: str = "fte",
+                       out_dir_prefix: Optional[str] = None):
+    """The numbers of the reference's `compare_traj_error` (acinoset_misc.py:1202-1264) without its plots: position
+    error (mm) of the single-view and the data-driven single-view reconstructions against the multi-view one.
+    Returns {"single_view": (mpe, mpjpe), "data_driven": (mpe, mpjpe)}; entries whose file is missing are skipped."""
+    data_dir = params.data_dir if out_dir_prefix is None else os.path.join(
+        out_dir_prefix, params.data_dir.split("cheetah_videos")[1][1:])
+    _ = (include_kinetic, kinetic_out_fname)
+    paths = dict(multi=os.path.join(data_dir, "fte_kinematic", "fte.pickle"),
+                 single_view=os.path.join(data_dir, f"fte_kinematic_orig_{scene.cam_idx}", "fte.pickle"),
+                 data_driven=os.path.join(data_dir, f"fte_kinematic_{scene.cam_idx}", "fte.pickle"))
+    if not os.path.exists(paths["multi"]):
+        return {}
+    with open(paths["multi"], "rb") as f:
+        gt = pickle.load(f)["positions"]
+    out = {}
+    for key in ("single_view", "data_driven"):
+        if not os.path.exists(paths[key]):
+            continue
+        with open(paths[key], "rb") as f:
+            pos = pickle.load(f)["positions"]
+        out[key] = (float(traj_error(gt.copy(), pos.copy()).mean()), float(traj_error(gt.copy(), pos.copy(), True).mean()))
+        print(f"{key}: MPE {out[key][0]:.1f} mm, MPJPE {out[key][1]:.1f} mm")
+    return out

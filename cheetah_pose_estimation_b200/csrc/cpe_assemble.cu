@@ -67,6 +67,7 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
 
     const bool mvalid = tid < TPF;
     const int mc = tid / 24, ml = tid - mc * 24;
+    const int ncam_s = p.b.n_cams ? p.b.n_cams[s] : C;      // cameras beyond it are padding of a ragged batch (weight 0)
     const size_t midx0 = ((fidx * C + mc) * 24 + ml) * W;
     MeasRaw mraw;
     mraw.d = make_double4(0.0, 0.0, 0.0, 0.0);
@@ -197,7 +198,7 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
             if (w > 0) meas_fetch(p.b, midx0 + w, mraw);
             meas_unpack(p.b, mraw, um, vm, gate);
             const bool sq = p.b.loss_mode == CPE_LOSS_SQUARE;
-            const double wgt = gate * p.m.meas_w[w * 24 + ml] * (sq ? 1.0 : cmult);
+            const double wgt = (mc < ncam_s ? gate : 0.0) * p.m.meas_w[w * 24 + ml] * (sq ? 1.0 : cmult);
             const double eu = wgt * (pr.u - um), ev = wgt * (pr.v - vm);
             const double Eu = fabs(eu), Ev = fabs(ev);
             double du_, dv_, wu_, wv_;

@@ -133,6 +133,7 @@ __global__ void __launch_bounds__(WPC * 32, MINB) eval_kernel(const __grid_const
     __syncthreads();                                       // the only CTA-wide barrier
     const int nf = p.b.n_frames[s];
     if (k >= nf) return;
+    const int TPFs = p.b.n_cams ? min(p.b.n_cams[s], C) * 24 : TPF;     // pairs of the real cameras (ragged batch)
     double *wd = reinterpret_cast<double *>(smraw + p.off_warp + warp * p.wbytes);
     T *wt = reinterpret_cast<T *>(wd + (CMP ? WD_C : WD));
     const T *sct = F64 ? reinterpret_cast<const T *>(wd + SCO) : wt;
@@ -291,6 +292,7 @@ __global__ void __launch_bounds__(WPC * 32, MINB) eval_kernel(const __grid_const
                     // residual = (fx a s) + (cx - u_meas): the ~1000 px offsets cancel in FP64 before rounding to T
                     const T ru = pr.pu + (T)(cx - um), rv = pr.pv + (T)(cy - vm);
                     if (p.eo.resid) reinterpret_cast<T2 *>(p.eo.resid)[mi + w] = mk2(ru, rv);
+                    if (pi >= TPFs) continue;                   // padding camera: rho(0) != 0 must not be counted
                     if (sq) {
                         rho += (wgt * ru) * (wgt * ru) + (wgt * rv) * (wgt * rv);
                     } else {

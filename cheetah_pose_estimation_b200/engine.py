@@ -19,6 +19,9 @@ _I32_KEYS = ("chain_link", "eq_pairs", "ineq_idx", "ind_idx", "ind_pos", "grp_nd
              "u_off", "u_item", "col_item", "ent_pq", "a_ptr", "a_items", "e_ptr", "e_items", "i_ptr", "i_items", "diag_ent",
              "grad_ent", "grp_src", "s_src", "s_ptr", "s_items", "ent_order", "s_order")
 _F64_KEYS = ("ineq_bounds", "wq", "meas_w")
+# penalty continuation of the augmented-Lagrangian outer loop: rounds 1-4 as in round 1 (the bench's LM leg runs 4);
+# the mirrored API runs 8, whose 1e7 rounds bring the joint equalities to ~1e-6, the level of the shipped IPOPT optima
+MU_SCHEDULE = (1e4, 1e5, 1e6, 1e6, 1e7, 1e7, 1e7, 1e7)
 
 
 def _ptr(t):
@@ -78,6 +81,7 @@ class Batch:
     shutter_tau: torch.Tensor = None   # [S,C] f64 seconds
     base_dq: torch.Tensor = None       # [S,N,3] f64
     base_ddq: torch.Tensor = None      # [S,N,3] f64
+    n_cams: torch.Tensor = None        # [S] int32, optional: cameras c >= n_cams[s] are padding (ragged batch)
 
     @property
     def meas_layout(self):
@@ -122,6 +126,9 @@ class Batch:
         b.lam_eq = self.lam_eq.data_ptr() if self.lam_eq is not None else None
         b.lam_in = self.lam_in.data_ptr() if self.lam_in is not None else None
         b.active = self.active.data_ptr() if self.active is not None else None
+        if self.n_cams is not None:
+            assert self.n_cams.is_cuda and self.n_cams.dtype == torch.int32 and self.n_cams.shape == (self.S,)
+            b.n_cams = self.n_cams.data_ptr()
         if self.shutter_tau is not None:
             for t, shp in ((self.shutter_tau, (self.S, self.C)), (self.base_dq, (self.S, self.N, 3)),
                            (self.base_ddq, (self.S, self.N, 3))):
@@ -142,11 +149,12 @@ class Batch:
                      active=None if self.active is None else self.active[s0:s1],
                      shutter_tau=None if self.shutter_tau is None else self.shutter_tau[s0:s1],
                      base_dq=None if self.base_dq is None else self.base_dq[s0:s1],
-                     base_ddq=None if self.base_ddq is None else self.base_ddq[s0:s1])
+                     base_ddq=None if self.base_ddq is None else self.base_ddq[s0:s1],
+                     n_cams=None if self.n_cams is None else self.n_cams[s0:s1])
 
     @staticmethod
     def from_numpy(meas, cams, chain_vec, h, n_frames=None, device="cuda", cam_model=FISHEYE, meas_dtype=torch.float32,
-                   dlc_native=False, dlc_thresh=0.5, loss_mode=LOSS_REDESCENDING):
+                   dlc_native=False, dlc_thresh=0.5, loss_mode=LOSS_REDESCENDING, n_cams=None):
         """meas[S,N,C,24,W,3|4] (u, v, gate), cams[S,C,24], chain_vec[S,24,5,3], h[S].  With dlc_native=True the
         last axis is the DLC triple (x, y, likelihood) and is kept as float3 records (gated on the device)."""
         meas = np.asarray(meas)
@@ -165,7 +173,8 @@ class Batch:
             meas=torch.as_tensor(np.ascontiguousarray(meas), device=dev).to(meas_dtype).contiguous(),
             cams=torch.as_tensor(np.ascontiguousarray(cams, dtype=np.float64), device=dev),
             chain_vec=torch.as_tensor(np.ascontiguousarray(chain_vec, dtype=np.float64), device=dev),
-            cam_model=cam_model, dlc_thresh=dlc_thresh, loss_mode=loss_mode)
+            cam_model=cam_model, dlc_thresh=dlc_thresh, loss_mode=loss_mode,
+            n_cams=None if n_cams is None else torch.as_tensor(np.asarray(n_cams, np.int32), device=dev))
 
 
 class Solver:
@@ -375,7 +384,7 @@ class Solver:
             pass
         return self.result
 
-    def solve_steps(self, q0, max_iter=40, n_outer=4, damp0=1e-3, ftol=1e-6, mu_schedule=(1e4, 1e5, 1e6, 1e6),
+    def solve_steps(self, q0, max_iter=40, n_outer=4, damp0=1e-3, ftol=1e-6, mu_schedule=MU_SCHEDULE,
                     check_every=1, skip_converged=True):
         """Generator form of `solve`: yields after the launches of every LM iteration have been queued (before the
         host looks at the convergence flags), so that a driver can interleave several solvers on different streams
@@ -484,7 +493,7 @@ class Solver:
         return g_tau, curv
 
     def solve_shutter(self, q0, tau0=None, max_iter=40, n_outer=4, damp0=1e-3, ftol=1e-7,
-                      mu_schedule=(1e4, 1e5, 1e6, 1e6), fix_first=True):
+                      mu_schedule=MU_SCHEDULE, fix_first=True):
         """Multi-view reconstruction WITH shutter-delay estimation (`shutter_delay_estimation=True`): minimises the same
         objective as `solve` over q and the per-camera delays tau[S,C] (camera 1 fixed at 0, |tau| <= 1/fps, as
         acinoset_misc.py:183, 274-275).  Each LM iteration takes ONE joint step from one assembly at (q, tau): the

@@ -90,11 +90,11 @@ def reduce_max(value, device, group=None):
 
 
 def gather_results(shard: ShardInfo, n_sequences, tensors, dst=0, group=None):
-    """Gather per-sequence results to rank `dst` in GLOBAL sequence order.
+    """Gather per-sequence results to rank `dst` (None = to every rank) in GLOBAL sequence order.
 
     tensors: dict name -> tensor [S_local, ...] (same trailing shape and dtype on every rank).  Shards may differ in
     size, so each rank's block is padded to the largest shard for the all_gather and trimmed afterwards.
-    Returns dict name -> tensor [n_sequences, ...] on `dst`, None elsewhere."""
+    Returns dict name -> tensor [n_sequences, ...] on `dst` (on every rank when dst is None), None elsewhere."""
     world = shard.world_size
     if world == 1 or not dist.is_initialized():
         out = {}
@@ -114,13 +114,14 @@ def gather_results(shard: ShardInfo, n_sequences, tensors, dst=0, group=None):
     idx_pad[:len(shard.index)] = torch.as_tensor(shard.index, device=dev)
     idx_all = [torch.empty_like(idx_pad) for _ in range(world)]
     dist.all_gather(idx_all, idx_pad, group=group)
-    out = {} if shard.rank == dst else None
+    keep = dst is None or shard.rank == dst
+    out = {} if keep else None
     for k, t in tensors.items():
         pad = torch.zeros((n_max,) + tuple(t.shape[1:]), dtype=t.dtype, device=dev)
         pad[:t.shape[0]] = t
         parts = [torch.empty_like(pad) for _ in range(world)]
         dist.all_gather(parts, pad, group=group)
-        if shard.rank == dst:
+        if keep:
             full = torch.empty((n_sequences,) + tuple(t.shape[1:]), dtype=t.dtype, device=dev)
             for r in range(world):
                 full[idx_all[r][:sizes[r]]] = parts[r][:sizes[r]]

@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 110          /* 0.1.10 */
+#define CPE_VERSION 111          /* 0.1.11 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -138,6 +138,12 @@ typedef struct cpe_batch {
     const double *shutter_tau;      /* [S,C] seconds; the reference fixes camera 1 at 0 and bounds the rest by +-1/fps */
     const double *base_dq;          /* [S,N,3] velocity of base x, y, z     (robot["base"]["dq"][n, 1, .]) */
     const double *base_ddq;         /* [S,N,3] acceleration of base x, y, z (robot["base"]["ddq"][n, 1, .]) */
+    /* Ragged camera count (the clips of data/test_set have 4, 5 or 6 cameras; acinoset_misc.py:171-174 makes C
+       per-clip data): cameras c >= n_cams[s] of sequence s are PADDING.  Their residuals are still written (layout
+       stays [.., C, ..]) but they add nothing to the cost, the gradient or the curvature, and because they sit behind
+       the real cameras every sum keeps the order of the unpadded problem: results are bit-identical to a batch with
+       C = n_cams[s].  The padded cams[] rows must still hold a valid camera.  NULL = C cameras for every sequence. */
+    const int32_t *n_cams;          /* [S] optional */
 } cpe_batch;
 
 /* Optional outputs of cpe_eval (NULL = skip). */

@@ -211,3 +211,28 @@ def test_shutter_delay_residuals_match_reference_expression(golden_dir):
               - cost.residuals(pb, clip["q"], g["tau"] - d, clip["dq"][:, 0:3], clip["ddq"][:, 0:3]))[:, :, :, 0, :] / (2 * eps)
         assert np.abs(fd[:, c] - J[:, c]).max() <= 1e-6 * np.abs(J[:, c]).max()
         assert np.abs(np.delete(fd, c, axis=1)).max() == 0.0
+
+
+def test_oracle_residuals_match_every_shipped_multi_view_clip(golden_dir):
+    """All 15 multi-view clips of the reference's data/test_set (10 AcinoSet fisheye, 5 kinetic-dataset pinhole),
+    cameras / detections rebuilt by oracle/make_golden_clips.py with the reference's own pt3d_to_2d[_fisheye]: the
+    oracle's FK reproduces the saved `positions` and its residuals the saved `meas_err` at the shipped optimum
+    (AcinoSet detections are stored as float32 -> half a float32 ulp of a pixel coordinate; kinetic ones in double)."""
+    g = _load(golden_dir, "test_set_clips.npz")
+    names = list(g["names"])
+    assert len(names) == 15
+    for i, nm in enumerate(names):
+        kin = bool(g[f"{i}_kinetic"])
+        lengths, radii, _ = tables.animal(str(g[f"{i}_animal"]))
+        cl, cv = kinematics.marker_chains(lengths, radii)
+        q, det, cams = g[f"{i}_q"], g[f"{i}_detections"], g[f"{i}_cams"]
+        assert float(g[f"{i}_rms"].max()) < 1e-8, nm                      # camera recovery converged
+        pos = kinematics.fk(q, cl, cv)
+        assert np.abs(pos - g[f"{i}_positions"]).max() < 1e-13, nm
+        N, C = det.shape[:2]
+        meas = np.concatenate([det.astype(np.float64)[:, :, :, None, :], np.ones((N, C, 24, 1, 1))], -1)
+        pb = cost.Problem(meas=meas, cams=cams, chain_link=cl, chain_vec=cv, h=1.0 / float(g[f"{i}_fps"]),
+                          cam_model=cameras.PINHOLE if kin else cameras.FISHEYE)
+        r = cost.residuals(pb, q)[:, :, :, 0, :]
+        tol = 1e-9 if kin else 2e-4
+        assert np.abs(r - g[f"{i}_meas_err"][..., 0]).max() < tol, (nm, np.abs(r - g[f"{i}_meas_err"][..., 0]).max())

@@ -35,6 +35,8 @@ def _worker(rank, world, port, n_seq, ragged, q_out):
         stats = sharding.reduce_stats(sharding.local_stats(cost, counters, converged=torch.ones(len(sh.index))))
         tmax = sharding.reduce_max(10.0 + rank, torch.device("cpu"))
         out = sharding.gather_results(sh, n_seq, {"q": q, "cost": cost, "status": counters[:, 1].contiguous()})
+        everywhere = sharding.gather_results(sh, n_seq, {"q": q}, dst=None)       # the run_dataset driver's form
+        assert torch.equal(everywhere["q"][:, 0, 0], torch.arange(n_seq, dtype=torch.float64))
         if rank == 0:
             q_out.put((stats, tmax, out["q"][:, 0, 0].numpy().copy(), out["cost"].numpy().copy(),
                        out["status"].numpy().copy(), len(sh.index)))

@@ -166,6 +166,87 @@ def test_hand_labelled_packing(tmp_path):
                     assert meas[n, c, l, 0, 2] == 1.0
 
 
+def _hand_label_csv(path, arr, first_frame, parts):
+    """DeepLabCut `CollectedData_<scorer>.csv` layout: 3 header rows, rows named by image path, (x, y) per part."""
+    import pandas as pd
+    cols = pd.MultiIndex.from_product([["scorer"], parts, ["x", "y"]], names=["scorer", "bodyparts", "coords"])
+    idx = [f"labeled-data/cam/img{first_frame + i:03d}.png" for i in range(arr.shape[0])]
+    pd.DataFrame(arr, columns=cols, index=idx).to_csv(path)
+
+
+def test_hand_labelled_initialisation(tmp_path):
+    """`hand_labeled_data=True` through the loaders and `create_trajectory_estimate` (acinoset_misc.py:381-456,
+    1545-1572): rows named by image file (frame = characters 3..5), (x, y) pairs per part, no likelihood filter, NaN
+    labels kept and weighted 0 in the spline.  A point moving on a straight line seen by two cameras must come back
+    as that line (spine + L_base / 2) with heading pi + atan2(dy, dx)."""
+    import cv2
+    rng = np.random.default_rng(11)
+    first, n_rows = 4, 16
+    parts = [f"part{i}" for i in range(25)]
+    for m, i in zip(sk.MARKERS, sk.DLC_INDEX):
+        parts[i] = m
+    spine = sk.DLC_INDEX[sk.MARKERS.index("spine")]
+    K = np.array([[900.0, 0, 960], [0, 900, 540], [0, 0, 1]])
+    D = np.zeros(4)
+    cams = []
+    for ang in (0.0, 0.5):
+        R = cv2.Rodrigues(np.array([0.0, ang, 0.0]))[0] @ cv2.Rodrigues(np.array([np.pi / 2, 0.0, 0.0]))[0]
+        t = -R @ np.array([[2.0 + 4 * ang], [-10.0], [1.0]])
+        cams.append((R, t))
+    frames = first + np.arange(n_rows)
+    track = np.stack([1.0 + 0.1 * frames, 0.3 + 0.02 * frames, 0.7 + 0 * frames], 1)
+    os.makedirs(tmp_path / "dlc_hand_labeled")
+    for c, (R, t) in enumerate(cams):
+        arr = rng.uniform(100, 900, (n_rows, 50))
+        uv = cv2.fisheye.projectPoints(track.reshape(-1, 1, 3), cv2.Rodrigues(R)[0], t, K, D)[0].reshape(-1, 2)
+        arr[:, 2 * spine], arr[:, 2 * spine + 1] = uv[:, 0], uv[:, 1]
+        if c == 1:
+            arr[6, 2 * spine] = arr[6, 2 * spine + 1] = np.nan              # an unlabelled frame
+        _hand_label_csv(tmp_path / "dlc_hand_labeled" / f"cam{c + 1}.csv", arr, first, parts)
+    data = misc.load_dlc_arrays(str(tmp_path / "dlc_hand_labeled"), 2, hand_labeled=True)
+    assert data.first_frame == [first, first] and data[0].shape == (n_rows, 50)
+    params = misc.TrajectoryParams(str(tmp_path), first, first + n_rows, n_rows, 0.5, None, True, False, False, False)
+    scene = misc.Scene("", np.stack([K, K]), np.stack([D, D]), np.stack([c[0] for c in cams]),
+                       np.stack([c[1] for c in cams]), (1920, 1080), 90, 2, None)
+    base_len = 0.4
+    x, y, z, psi = misc.create_trajectory_estimate(base_len, params, scene, False, data)
+    assert len(x) == first + n_rows
+    assert np.abs(x[frames] - (track[:, 0] + base_len / 2)).max() < 2e-3
+    assert np.abs(y[frames] - track[:, 1]).max() < 2e-3 and np.abs(z[frames] - track[:, 2]).max() < 2e-3
+    assert np.abs(psi[frames[:-1]] - (np.pi + np.arctan2(0.02, 0.1))).max() < 2e-2
+    # packing: hand-labelled rows are addressed by row position start_frame + n, not shifted by the sync offset
+    meas, _ = misc.pack_measurements(params, scene, DlcPad(data))
+    assert meas.shape == (n_rows, 2, 24, 1, 4)
+
+
+class DlcPad(list):
+    """Hand-labelled tables as the reference indexes them: row position = frame number (the shipped label files start at
+    frame 0); pads the fixture's rows to that layout."""
+
+    def __init__(self, data):
+        super().__init__(np.concatenate([np.full((f, a.shape[1]), np.nan), a]) for a, f in zip(data, data.first_frame))
+        self.first_frame = [0] * len(data)
+
+
+def test_dlc_rows_are_addressed_by_position_like_the_reference(tmp_path):
+    """`init_measurements` indexes `list(df.to_numpy())` by (n-1) + start_frame - sync (acinoset_misc.py:207, 224, 246): a
+    table whose index starts above 0 is NOT re-based for the packing, only for the trajectory initialisation."""
+    import pandas as pd
+    rng = np.random.default_rng(3)
+    arr = rng.uniform(0, 1000, (10, 75))
+    arr[:, 2::3] = 0.9
+    cols = pd.MultiIndex.from_product([["s"], [f"p{i}" for i in range(25)], ["x", "y", "likelihood"]])
+    os.makedirs(tmp_path / "dlc")
+    pd.DataFrame(arr, columns=cols, index=np.arange(5, 15)).to_csv(tmp_path / "dlc" / "cam1.csv")
+    data = misc.load_dlc_arrays(str(tmp_path / "dlc"), 1)
+    assert data.first_frame == [5] and data[0].shape == (10, 75)
+    params = misc.TrajectoryParams(str(tmp_path), 2, 6, 4, 0.5, None, False, False, False, False)
+    scene = misc.Scene("", None, None, None, None, None, 90, 1, None)
+    meas, _ = misc.pack_measurements(params, scene, data)
+    l = 4
+    assert meas[0, 0, l, 0, 0] == np.float32(arr[2, 3 * sk.DLC_INDEX[l]])
+
+
 def test_base_rates_match_the_oracle_and_the_collocation_rows():
     """engine.base_rates (host-side torch plumbing of the shutter-delay driver) against the oracle's restatement, on a
     ragged batch, and against the implicit-Euler rows it eliminates (collocation.py:58-68)."""

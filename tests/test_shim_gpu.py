@@ -9,7 +9,7 @@ import pickle
 import numpy as np
 import pytest
 
-from tests._dataset import build_clip_dir
+from tests._dataset import build_clip_dir, write_data_driven_dataset as _write_data_driven_dataset
 
 pytestmark = pytest.mark.gpu
 
@@ -54,23 +54,6 @@ def test_kinematic_reconstruction_of_a_real_clip(golden_dir, tmp_path, animal, f
           f"obj_cost {float(g['obj_cost']):.3f} with the lost mask), MPJPE {mpjpe:.1f} mm, MPE {mpe:.1f} mm, "
           f"{d['processing_time_s']:.3f} s vs IPOPT {float(g['processing_time_s']):.1f} s")
     assert mpjpe < 30.0 and mpe < 60.0
-
-
-def _write_data_driven_dataset(golden_dir, models_dir):
-    """A stand-in for the reference's models/data-driven/dataset_full_pose.csv (which does not travel to the GPU box):
-    the reduced poses `x` of the reference's shipped trajectories (tests/golden/shipped_clips.npz), one segment per
-    clip, index restarting at 0 -- the same table layout (28 pose columns, 28 derivative columns)."""
-    import pandas as pd
-    g = np.load(os.path.join(golden_dir, "shipped_clips.npz"))
-    rows, idx = [], []
-    for key in sorted((k for k in g.keys() if k.endswith("_x")), key=lambda k: int(k.split("_")[0])):
-        x = g[key]
-        if x.shape[0] < 9:
-            continue
-        rows.append(np.concatenate([x, np.gradient(x, axis=0)], axis=1))
-        idx.append(np.arange(x.shape[0]))
-    os.makedirs(models_dir, exist_ok=True)
-    pd.DataFrame(np.concatenate(rows), index=np.concatenate(idx)).to_csv(os.path.join(models_dir, "dataset_full_pose.csv"))
 
 
 def test_monocular_reconstruction_with_data_driven_priors(golden_dir, tmp_path):
