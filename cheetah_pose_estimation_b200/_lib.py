@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libcpe_b200.so")
+# CPE_LIB_PATH: another build of the same ABI (A/B timing of kernel variants); never a fallback
+LIB_PATH = os.environ.get("CPE_LIB_PATH") or os.path.join(_HERE, "libcpe_b200.so")
 
 c_i32p = C.c_void_p
 c_f64p = C.c_void_p
@@ -23,6 +24,8 @@ class CpeModel(C.Structure):
         ("ent_pq", c_i32p), ("a_ptr", c_i32p), ("a_items", c_i32p), ("e_ptr", c_i32p), ("e_items", c_i32p),
         ("i_ptr", c_i32p), ("i_items", c_i32p), ("diag_ent", c_i32p), ("grad_ent", c_i32p), ("grp_src", c_i32p),
         ("s_src", c_i32p), ("s_ptr", c_i32p), ("s_items", c_i32p), ("ent_order", c_i32p), ("s_order", c_i32p),
+        ("ent_meta", c_i32p), ("a_ell", c_i32p), ("e_ell", c_i32p), ("i_ell", c_i32p), ("s_meta", c_i32p),
+        ("s_ell", c_i32p),
     ]
 
 

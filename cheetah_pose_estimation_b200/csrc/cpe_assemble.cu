@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
     extern __shared__ __align__(16) double sm[];
     const int tid = threadIdx.x, nt = blockDim.x;
     const int N = p.b.N, C = p.b.C, W = p.b.W, TPF = p.TPF;
-    const int s = blockIdx.y, k = blockIdx.x;
+    const int s = blockIdx.x / N, k = blockIdx.x - s * N;      // 1-D grid: S is not bound by the 65535 of grid.y
     const int nf = p.b.n_frames[s];
     if (k >= nf || (p.b.active && !p.b.active[s])) return;
     const size_t fidx = (size_t)s * N + k;
@@ -262,40 +262,47 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
     }
     __syncthreads();
     // ---- every Hessian / gradient nonzero = one gather over its static item list -------------------------------------
-    for (int eo = tid; eo < n_ent; eo += nt) {
-        const int e = p.m.ent_order[eo];                 // lanes of a warp get gather lists of similar length
-        const int pq = p.m.ent_pq[e];
-        const int pp = pq >> 6, qq = pq & 63;
-        const bool grad = qq == GRAD_Q;
-        double acc = 0.0;
-        for (int i = p.m.a_ptr[e], i1 = p.m.a_ptr[e + 1]; i < i1; ++i) {
-            const int it = p.m.a_items[i];
-            const double *g = GV + (it >> 16), *b = BV + (it & 0xFFFF);
-            acc += g[0] * b[0] + g[1] * b[1] + g[2] * b[2];
+    // slot-major tables (skeleton.ell_tables): lane <-> consecutive eo, so every table load of a warp is one line and
+    // no load address depends on a loaded index
+    {
+        const uint2 *meta = reinterpret_cast<const uint2 *>(p.m.ent_meta);
+        const int32_t *a_ell = p.m.a_ell, *e_ell = p.m.e_ell, *i_ell = p.m.i_ell;
+        for (int eo = tid; eo < n_ent; eo += nt) {
+            const uint2 m = meta[eo];
+            const int e = m.x & 1023, pp = (m.x >> 10) & 63, qq = (m.x >> 16) & 63;
+            const int na = m.y & 255, ne = (m.y >> 8) & 255, ni = m.y >> 16;
+            const bool grad = qq == GRAD_Q;
+            double acc = 0.0;
+#pragma unroll 4
+            for (int i = 0; i < na; ++i) {
+                const int it = a_ell[i * CPE_ELL_ENT + eo];
+                const double *g = GV + (it >> 16), *b = BV + (it & 0xFFFF);
+                acc += g[0] * b[0] + g[1] * b[1] + g[2] * b[2];
+            }
+            double acce = 0.0;
+            for (int i = 0; i < ne; ++i) {
+                const int it = e_ell[i * CPE_ELL_ENT + eo];
+                const double gi = fr[A_EQG + (it >> 8)];
+                acce += gi * (grad ? fr[A_EQR + (it & 255)] : mu_eq * fr[A_EQG + (it & 255)]);
+            }
+            double acci = 0.0;
+            for (int i = 0; i < ni; ++i) {
+                const int it = i_ell[i * CPE_ELL_ENT + eo];
+                const double v = fr[A_VIN + (it >> 1)];
+                const double val = grad ? v : (v != 0.0 ? 1.0 : 0.0);
+                acci += (it & 1) ? -val : val;
+            }
+            acc += acce + mu_in * acci;
+            if (grad) {
+                acc += fr[A_MOG + pp];
+                if (p.ao.g) p.ao.g[fidx * 54 + pp] = acc;
+            } else if (p.ao.Hraw) {
+                double *o = p.ao.Hraw + fidx * 54 * 54;
+                o[pp * 54 + qq] = acc;
+                o[qq * 54 + pp] = acc;
+            }
+            ENT[e] = acc;
         }
-        double acce = 0.0;
-        for (int i = p.m.e_ptr[e], i1 = p.m.e_ptr[e + 1]; i < i1; ++i) {
-            const int it = p.m.e_items[i];
-            const double gi = fr[A_EQG + (it >> 8)];
-            acce += gi * (grad ? fr[A_EQR + (it & 255)] : mu_eq * fr[A_EQG + (it & 255)]);
-        }
-        double acci = 0.0;
-        for (int i = p.m.i_ptr[e], i1 = p.m.i_ptr[e + 1]; i < i1; ++i) {
-            const int it = p.m.i_items[i];
-            const double v = fr[A_VIN + (it >> 1)];
-            const double val = grad ? v : (v != 0.0 ? 1.0 : 0.0);
-            acci += (it & 1) ? -val : val;
-        }
-        acc += acce + mu_in * acci;
-        if (grad) {
-            acc += fr[A_MOG + pp];
-            if (p.ao.g) p.ao.g[fidx * 54 + pp] = acc;
-        } else if (p.ao.Hraw) {
-            double *o = p.ao.Hraw + fidx * 54 * 54;
-            o[pp * 54 + qq] = acc;
-            o[qq * 54 + pp] = acc;
-        }
-        ENT[e] = acc;
     }
     __syncthreads();
     const double h4 = h * h * h * h;
@@ -352,19 +359,15 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
     __syncthreads();
     // ---- reduced block S = H_ii + damping - sum_g Hdi^T Y and ghat = g_i - sum_g Hdi^T y (static gather) ----------------
     double *So = p.ao.S + fidx * 784;
+    const uint32_t *s_meta = p.m.s_meta;
+    const int32_t *s_ell = p.m.s_ell;
     for (int eo = tid; eo < 28 * 29; eo += nt) {
-        const int e = p.m.s_order[eo];
-        const int r = e / 29, c = e - r * 29;
-        double v;
-        if (c == 28) {
-            v = ENT[p.m.grad_ent[p.m.ind_idx[r]]];
-        } else {
-            const int si = p.m.s_src[r * 28 + c];
-            v = si >= 0 ? ENT[si] : 0.0;
-            if (r == c) v += damp * fr[A_DIAG + p.m.ind_idx[r]];
-        }
-        for (int i = p.m.s_ptr[e], i1 = p.m.s_ptr[e + 1]; i < i1; ++i) {
-            const int it = p.m.s_items[i];
+        const uint32_t m = s_meta[eo];
+        const int r = m & 31, c = (m >> 5) & 31, ns = (m >> 10) & 7, si = m >> 13;
+        double v = si != 1023 ? ENT[si] : 0.0;
+        if (r == c) v += damp * fr[A_DIAG + p.m.ind_idx[r]];
+        for (int i = 0; i < ns; ++i) {
+            const int it = s_ell[i * CPE_ELL_S + eo];
             const int g = it >> 8, a = (it >> 4) & 15, b = it & 15;
             const double *D = DDI + g * GD * GN + a;
             const double *Yc = YS + g * GD * (GN + 1) + (b == 15 ? GN : b);
@@ -398,11 +401,11 @@ extern "C" int cpe_assemble_f64(const cpe_model *model, const cpe_batch *b, cons
     using namespace cpe;
     if (!model || !b || !q || !out) return CPE_E_NULL;
     if (b->S <= 0 || b->N <= 0 || b->C <= 0 || b->C > CPE_MAX_CAMS || (b->W != 1 && b->W != 3)) return CPE_E_DIM;
-    if (b->S > 65535 || model->n_ineq > CPE_MAX_INEQ || model->n_groups > CPE_MAX_GROUPS) return CPE_E_DIM;
+    if ((long long)b->S * b->N > 2147483647LL || model->n_ineq > CPE_MAX_INEQ || model->n_groups > CPE_MAX_GROUPS)
+        return CPE_E_DIM;
     if (model->n_u != 198 || model->n_ent <= 0 || model->n_ent > ENT_PAD) return CPE_E_DIM;
-    if (!model->ent_pq || !model->a_ptr || !model->a_items || !model->e_ptr || !model->e_items || !model->i_ptr ||
-        !model->i_items || !model->diag_ent || !model->grad_ent || !model->grp_src || !model->s_src || !model->s_ptr ||
-        !model->s_items || !model->ent_order || !model->s_order)
+    if (!model->ent_meta || !model->a_ell || !model->e_ell || !model->i_ell || !model->s_meta || !model->s_ell ||
+        !model->diag_ent || !model->grp_src || !model->grp_dep || !model->ind_idx)
         return CPE_E_NULL;
     if (out->S && (!damp || !out->ghat || !out->Y || !out->y)) return CPE_E_NULL;
     if ((b->shutter_tau || b->base_dq || b->base_ddq) && !(b->shutter_tau && b->base_dq && b->base_ddq)) return CPE_E_NULL;
@@ -416,7 +419,7 @@ extern "C" int cpe_assemble_f64(const cpe_model *model, const cpe_batch *b, cons
     const size_t smem = (size_t)(b->C * CPE_CAM_STRIDE + A_AT + p.at_size) * sizeof(double);
     int threads = ((p.TPF + 31) / 32) * 32;
     if (threads < 160) threads = 160;               // >= 5 warps: one per elimination group
-    const dim3 grid(b->N, b->S, 1);
+    const dim3 grid((unsigned)(b->N * b->S), 1, 1);
     if (threads <= 160) return launch_asm<160, 6>(p, grid, threads, smem, (cudaStream_t)stream);
     return launch_asm<192, 4>(p, grid, threads, smem, (cudaStream_t)stream);
 }

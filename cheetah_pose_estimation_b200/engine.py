@@ -17,7 +17,8 @@ MEAS_F32X4, MEAS_F64X4, MEAS_F32X3 = 0, 1, 2      # include/cpe.h CPE_MEAS_*
 LOSS_REDESCENDING, LOSS_SQUARE = 0, 1             # include/cpe.h CPE_LOSS_*
 _I32_KEYS = ("chain_link", "eq_pairs", "ineq_idx", "ind_idx", "ind_pos", "grp_ndep", "grp_nnb", "grp_dep", "grp_nb",
              "u_off", "u_item", "col_item", "ent_pq", "a_ptr", "a_items", "e_ptr", "e_items", "i_ptr", "i_items", "diag_ent",
-             "grad_ent", "grp_src", "s_src", "s_ptr", "s_items", "ent_order", "s_order")
+             "grad_ent", "grp_src", "s_src", "s_ptr", "s_items", "ent_order", "s_order", "ent_meta", "a_ell", "e_ell",
+             "i_ell", "s_meta", "s_ell")
 _F64_KEYS = ("ineq_bounds", "wq", "meas_w")
 # penalty continuation of the augmented-Lagrangian outer loop: rounds 1-4 as in round 1 (the bench's LM leg runs 4);
 # the mirrored API runs 8, whose 1e7 rounds bring the joint equalities to ~1e-6, the level of the shipped IPOPT optima

@@ -467,7 +467,54 @@ def assemble_tables(t=None, kinetic_dataset=False):
     work = 3 * np.diff(a_ptr) + np.diff(e_ptr) + np.diff(i_ptr)
     ent_order = np.argsort(-work, kind="stable").astype(np.int32)
     s_order = np.argsort(-np.diff(s_ptr), kind="stable").astype(np.int32)
-    return dict(n_ent=len(keys), ent_pq=ent_pq, a_ptr=a_ptr, a_items=a_items, e_ptr=e_ptr, e_items=e_items,
-                i_ptr=i_ptr, i_items=i_items, diag_ent=diag_ent, grad_ent=grad_ent, grp_src=grp_src.reshape(-1),
-                s_src=s_src.reshape(-1), s_ptr=s_ptr, s_items=np.array(s_items, np.int32), ent_order=ent_order,
-                s_order=s_order)
+    out = dict(n_ent=len(keys), ent_pq=ent_pq, a_ptr=a_ptr, a_items=a_items, e_ptr=e_ptr, e_items=e_items,
+               i_ptr=i_ptr, i_items=i_items, diag_ent=diag_ent, grad_ent=grad_ent, grp_src=grp_src.reshape(-1),
+               s_src=s_src.reshape(-1), s_ptr=s_ptr, s_items=np.array(s_items, np.int32), ent_order=ent_order,
+               s_order=s_order)
+    out.update(ell_tables(out, t["ind_idx"]))
+    return out
+
+
+ELL_ENT, ELL_S = 640, 832           # row strides of the slot-major tables (include/cpe.h CPE_ELL_*)
+ELL_A_SLOTS, ELL_E_SLOTS, ELL_I_SLOTS, ELL_S_SLOTS = 24, 5, 4, 5
+
+
+def ell_tables(a, ind_idx):
+    """The same gather lists in the layout K2 reads: one packed word per work item IN PROCESSING ORDER and the list
+    items slot-major (`a_ell[slot * ELL_ENT + eo]`), so that the 32 lanes of a warp, which work on consecutive `eo`,
+    load consecutive words and no load address depends on a previously loaded index (the CSR form costs three dependent
+    global loads per entry: order -> pointer -> item).  The order of the items inside a list is unchanged, hence every
+    sum is bit-identical to the CSR walk.
+        ent_meta[eo] = (e | p << 10 | q << 16,  n_a | n_e << 8 | n_i << 16)
+        s_meta[eo]   = r | c << 5 | n_s << 10 | src << 13     (src = entry holding H(ind_r, ind_c) or g(ind_r); 1023 = none)"""
+    n_ent = int(a["n_ent"])
+    assert n_ent <= ELL_ENT and n_ent < 1024
+    ent_meta = np.zeros((ELL_ENT, 2), np.uint32)
+    a_ell = np.zeros((ELL_A_SLOTS, ELL_ENT), np.int32)
+    e_ell = np.zeros((ELL_E_SLOTS, ELL_ENT), np.int32)
+    i_ell = np.zeros((ELL_I_SLOTS, ELL_ENT), np.int32)
+    for eo, e in enumerate(a["ent_order"]):
+        e = int(e)
+        pq = int(a["ent_pq"][e])
+        lists = []
+        for ptr, items, ell, cap in ((a["a_ptr"], a["a_items"], a_ell, ELL_A_SLOTS), (a["e_ptr"], a["e_items"], e_ell, ELL_E_SLOTS),
+                                     (a["i_ptr"], a["i_items"], i_ell, ELL_I_SLOTS)):
+            lst = items[int(ptr[e]):int(ptr[e + 1])]
+            assert len(lst) <= cap
+            ell[:len(lst), eo] = lst
+            lists.append(len(lst))
+        ent_meta[eo] = (e | ((pq >> 6) << 10) | ((pq & 63) << 16), lists[0] | (lists[1] << 8) | (lists[2] << 16))
+    n_s = N_IND * (N_IND + 1)
+    assert n_s <= ELL_S
+    s_meta = np.zeros(ELL_S, np.uint32)
+    s_ell = np.zeros((ELL_S_SLOTS, ELL_S), np.int32)
+    for eo, e in enumerate(a["s_order"]):
+        e = int(e)
+        r, c = divmod(e, N_IND + 1)
+        lst = a["s_items"][int(a["s_ptr"][e]):int(a["s_ptr"][e + 1])]
+        assert len(lst) <= ELL_S_SLOTS
+        s_ell[:len(lst), eo] = lst
+        src = int(a["grad_ent"][int(ind_idx[r])]) if c == N_IND else int(a["s_src"][r * N_IND + c])
+        s_meta[eo] = r | (c << 5) | (len(lst) << 10) | ((src if src >= 0 else 1023) << 13)
+    return dict(ent_meta=ent_meta.view(np.int32).reshape(-1), a_ell=a_ell.reshape(-1), e_ell=e_ell.reshape(-1),
+                i_ell=i_ell.reshape(-1), s_meta=s_meta.view(np.int32), s_ell=s_ell.reshape(-1))

@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 111          /* 0.1.11 */
+#define CPE_VERSION 112          /* 0.1.12 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -51,6 +51,8 @@ extern "C" {
 #define CPE_GRP_MAX_NB 12        /* ... coupled to <= 12 independent coords */
 #define CPE_MAX_GROUPS 8
 #define CPE_COST_TERMS 4         /* measurement, model, al_eq, al_in */
+#define CPE_ELL_ENT 640          /* row stride of cpe_model.a_ell / e_ell / i_ell (>= n_ent) */
+#define CPE_ELL_S 832            /* row stride of cpe_model.s_ell (>= 28 * 29) */
 
 #define CPE_CAM_FISHEYE 0        /* acinoset_misc.py:1663-1679 */
 #define CPE_CAM_PINHOLE 1        /* acinoset_misc.py:1682-1696 */
@@ -107,6 +109,15 @@ typedef struct cpe_model {
     const int32_t *s_items;
     const int32_t *ent_order;       /* [n_ent] processing order of the entries, longest gather list first */
     const int32_t *s_order;         /* [28*29] processing order of the Schur items, longest list first */
+    /* The same lists in the layout K2 reads (skeleton.ell_tables): one packed word per work item in processing order,
+       list items slot-major, so consecutive lanes load consecutive words and no address depends on a loaded index.
+       The CSR tables above remain the definition (tests/test_assemble_tables.py checks both against each other). */
+    const uint32_t *ent_meta;       /* [CPE_ELL_ENT][2] { e | p << 10 | q << 16,  n_a | n_e << 8 | n_i << 16 } */
+    const int32_t *a_ell;           /* [24][CPE_ELL_ENT] */
+    const int32_t *e_ell;           /* [5][CPE_ELL_ENT] */
+    const int32_t *i_ell;           /* [4][CPE_ELL_ENT] */
+    const uint32_t *s_meta;         /* [CPE_ELL_S] r | c << 5 | n_s << 10 | src << 13 (src 1023 = structural zero) */
+    const int32_t *s_ell;           /* [5][CPE_ELL_S] */
 } cpe_model;
 
 /* One batch of sequences. */

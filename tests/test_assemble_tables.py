@@ -121,3 +121,34 @@ def test_tables_reproduce_oracle_normal_equations():
     S_ref, ghat_ref, _, _ = lm.schur_frames(H, g, diagH, damp)
     assert np.abs(S - S_ref).max() <= 1e-9 * np.abs(S_ref).max()
     assert np.abs(ghat - ghat_ref).max() <= 1e-9 * np.abs(ghat_ref).max()
+
+
+def test_ell_tables_hold_the_same_lists_in_processing_order():
+    """skeleton.ell_tables (the slot-major layout K2 reads) against the CSR definition: same entries, same items in the
+    same order, processing order = ent_order / s_order."""
+    t = sk.build_tables(False)
+    at = sk.assemble_tables(t)
+    meta = at["ent_meta"].view(np.uint32).reshape(-1, 2)
+    for name, slots, ptr, items in (("a_ell", sk.ELL_A_SLOTS, "a_ptr", "a_items"), ("e_ell", sk.ELL_E_SLOTS, "e_ptr", "e_items"),
+                                    ("i_ell", sk.ELL_I_SLOTS, "i_ptr", "i_items")):
+        ell = at[name].reshape(slots, sk.ELL_ENT)
+        shift = {"a_ell": 0, "e_ell": 8, "i_ell": 16}[name]
+        for eo, e in enumerate(at["ent_order"]):
+            e = int(e)
+            assert int(meta[eo, 0] & 1023) == e
+            assert int((meta[eo, 0] >> 10) & 63) * 64 + int((meta[eo, 0] >> 16) & 63) == int(at["ent_pq"][e])
+            n = int((meta[eo, 1] >> shift) & 255)
+            lst = at[items][int(at[ptr][e]):int(at[ptr][e + 1])]
+            assert n == len(lst) and np.array_equal(ell[:n, eo], lst)
+    sm = at["s_meta"].view(np.uint32)
+    s_ell = at["s_ell"].reshape(sk.ELL_S_SLOTS, sk.ELL_S)
+    for eo, e in enumerate(at["s_order"]):
+        e = int(e)
+        r, c = divmod(e, 29)
+        m = int(sm[eo])
+        assert (m & 31, (m >> 5) & 31) == (r, c)
+        lst = at["s_items"][int(at["s_ptr"][e]):int(at["s_ptr"][e + 1])]
+        n = (m >> 10) & 7
+        assert n == len(lst) and np.array_equal(s_ell[:n, eo], lst)
+        src = int(at["grad_ent"][int(t["ind_idx"][r])]) if c == 28 else int(at["s_src"][r * 28 + c])
+        assert (m >> 13) == (src if src >= 0 else 1023)

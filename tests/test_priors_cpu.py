@@ -31,6 +31,19 @@ def test_oracle_reproduces_fixture_costs(gold):
     assert np.allclose(priors.motion_residuals(pr, gold["q"]), gold["motion_resid"], atol=1e-12)
 
 
+def test_gmm_pose_term_is_pinned_by_three_independent_evaluations(gold):
+    """Row a11: the oracle's per-frame pose cost against (i) the reference's OWN `norm_pdf_multivariate` (its source
+    cut out of misc.gmm_pose_cost and executed at fixture-generation time), (ii) scikit-learn's mixture density
+    (`-log(exp(score_samples) + 1e-12)`) and (iii) scipy's multivariate normal -- oracle/make_golden_priors.py."""
+    from oracle import priors
+    pr = _pr(gold)
+    q = gold["q"]
+    frame = np.array([priors.pose_cost(pr, q[k:k + 1]) for k in range(q.shape[0])])
+    for key in ("pose_frame_reference", "pose_frame_sklearn", "pose_frame_scipy"):
+        assert np.abs(frame - gold[key]).max() < 1e-10, key
+    assert abs(frame.sum() - gold["costs"][0]) < 1e-10
+
+
 def test_reduced_matrix_agrees_with_oracle_and_only_uses_prior_coordinates():
     from cheetah_pose_estimation_b200 import priors as pp, skeleton
     from oracle import priors

@@ -81,7 +81,9 @@ def test_monocular_reconstruction_with_data_driven_priors(golden_dir, tmp_path):
     mpjpe = misc.traj_error(d["positions"].copy(), g["positions"].copy(), centered=True).mean()
     print(f"monocular cam 0: obj {d['obj_cost']:.3f}, costs {est.costs}, MPJPE vs the shipped multi-view trajectory "
           f"{mpjpe:.1f} mm, {d['processing_time_s']:.3f} s")
-    assert mpjpe < 250.0
+    # the reference reports 64.7 mm (MPJPE, data-driven) for this clip (its own camera and its own
+    # training set); bound = 1.5 x that, the prior here being fitted on the 55 shipped trajectories only
+    assert mpjpe < 1.5 * 64.7
 
 
 def test_shutter_delay_estimation_through_the_mirrored_api(golden_dir, tmp_path):
