@@ -80,7 +80,9 @@ class CheetahEstimator:
         them to 5e-8 .. 9e-5 (tests/test_run_dataset_gpu.py prints both) -- and inequality violations below 5e-4 rad."""
         if results is None:
             return False
-        ok = int(results["status"]) == 0 and np.isfinite(results["cost"]).all()
+        # CPE_STATUS_PIVOT | CPE_STATUS_NONFINITE disqualify; CPE_STATUS_MAXITER alone does not (the feasibility test below
+        # decides, as IPOPT's "acceptable" termination does)
+        ok = (int(results["status"]) & 5) == 0 and np.isfinite(results["cost"]).all()
         return bool(ok and np.abs(results["c_eq"]).max() < CEQ_TOL and np.abs(results["v_in"]).max() < VIN_TOL)
 
     def estimate_grf(self, plot: bool = False, monocular: bool = False, out_dir_prefix: Optional[str] = None,

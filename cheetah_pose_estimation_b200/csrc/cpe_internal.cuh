@@ -91,7 +91,16 @@ __device__ __forceinline__ void meas_unpack(const cpe_batch &b, const MeasRaw &m
         u = m.d.x; v = m.d.y; gate = m.d.z;
     } else {
         u = (double)m.f.x; v = (double)m.f.y;
-        gate = b.meas_layout == CPE_MEAS_F32X4 ? (double)m.f.z : ((double)m.f.z > b.dlc_thresh ? 1.0 : 0.0);
+        if (b.meas_layout == CPE_MEAS_F32X4) {
+            gate = (double)m.f.z;
+        } else {
+            // DLC-native record, gated here: a NaN coordinate or likelihood gets gate 0 and a finite stand-in, so that it
+            // cannot poison the sums (the reference's own NaN guards are no-ops; the host packer of the
+            // pre-gated layouts does the same: acinoset_misc.pack_measurements)
+            const bool fin = (u == u) && (v == v);
+            gate = (fin && (double)m.f.z > b.dlc_thresh) ? 1.0 : 0.0;
+            if (!fin) { u = 0.0; v = 0.0; }
+        }
     }
 }
 

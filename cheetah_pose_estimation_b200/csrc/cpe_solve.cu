@@ -137,6 +137,20 @@ __global__ void __launch_bounds__(128) step_accept_kernel(int S, int N, const in
     }
 }
 
+// per-sequence exit status of an LM / AL solve (cpe.h CPE_STATUS_*)
+__global__ void finalize_status_kernel(int S, const double *cost, const double *cost_extra, const int32_t *active,
+                                       const int32_t *pivot, int32_t *status) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= S) return;
+    double f = cost[s * 4] + cost[s * 4 + 1] + cost[s * 4 + 2] + cost[s * 4 + 3];
+    if (cost_extra) f += cost_extra[s * 2] + cost_extra[s * 2 + 1];
+    int st = 0;
+    if (pivot && pivot[s]) st |= CPE_STATUS_PIVOT;
+    if (active && active[s]) st |= CPE_STATUS_MAXITER;
+    if (!(fabs(f) <= 1.7976931348623157e308)) st |= CPE_STATUS_NONFINITE;      // NaN or infinity
+    status[s] = st;
+}
+
 __global__ void update_multipliers_kernel(int S, int N, int n_ineq, const int32_t *n_frames, double mu_eq, double mu_in,
                                           const double *c_eq, const double *v_in, double *lam_eq, double *lam_in) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -191,6 +205,14 @@ extern "C" int cpe_step_accept_prior_f64(const cpe_batch *b, const double *cost_
     return (int)cudaGetLastError();
 }
 
+extern "C" int cpe_finalize_status_f64(const cpe_batch *b, const double *cost, const double *cost_extra,
+                                       const int32_t *active, const int32_t *pivot, int32_t *status, void *stream) {
+    if (!b || !cost || !status) return CPE_E_NULL;
+    cpe::finalize_status_kernel<<<(b->S + 127) / 128, 128, 0, (cudaStream_t)stream>>>(b->S, cost, cost_extra, active, pivot,
+                                                                                      status);
+    return (int)cudaGetLastError();
+}
+
 extern "C" int cpe_update_multipliers_f64(const cpe_model *model, const cpe_batch *b, const double *c_eq, const double *v_in,
                                           double *lam_eq, double *lam_in, void *stream) {
     if (!model || !b || !c_eq || !v_in || !lam_eq || !lam_in) return CPE_E_NULL;
@@ -203,18 +225,20 @@ extern "C" int cpe_update_multipliers_f64(const cpe_model *model, const cpe_batc
 extern "C" int cpe_eval_host_f64(const cpe_model *model, const cpe_batch *bd, const double *h_q, const void *h_meas,
                                  double *d_q, void *d_meas, const cpe_eval_out *out_dev, double *d_cost, double *h_cost,
                                  double *h_resid, void *stream) {
-    if (!model || !bd || !h_q || !h_meas || !d_q || !d_meas || !out_dev || !d_cost || !h_cost) return CPE_E_NULL;
-    if (!out_dev->frame_cost) return CPE_E_NULL;
+    if (!model || !bd || !h_q || !d_q || !out_dev || !d_cost || !h_cost) return CPE_E_NULL;
+    if (!out_dev->frame_cost || (h_meas && !d_meas) || (!h_meas && !bd->meas)) return CPE_E_NULL;
     cudaStream_t st = (cudaStream_t)stream;
     const size_t frames = (size_t)bd->S * bd->N;
     const size_t rec = bd->meas_layout == CPE_MEAS_F64X4 ? 32 : (bd->meas_layout == CPE_MEAS_F32X3 ? 12 : 16);
     const size_t mbytes = frames * bd->C * 24 * bd->W * rec;
     cudaError_t e = cudaMemcpyAsync(d_q, h_q, frames * 54 * sizeof(double), cudaMemcpyHostToDevice, st);
     if (e != cudaSuccess) return (int)e;
-    e = cudaMemcpyAsync(d_meas, h_meas, mbytes, cudaMemcpyHostToDevice, st);
-    if (e != cudaSuccess) return (int)e;
     cpe_batch b = *bd;
-    b.meas = d_meas;
+    if (h_meas) {                  // NULL: the detections are already resident in bd->meas (they do not change between
+        e = cudaMemcpyAsync(d_meas, h_meas, mbytes, cudaMemcpyHostToDevice, st);      // the iterations of a solve)
+        if (e != cudaSuccess) return (int)e;
+        b.meas = d_meas;
+    }
     int rc = cpe_eval_f64(model, &b, d_q, out_dev, stream);
     if (rc) return rc;
     rc = cpe_reduce_cost_f64(&b, out_dev->frame_cost, d_cost, stream);

@@ -15,6 +15,7 @@ from . import _lib, skeleton
 FISHEYE, PINHOLE = 0, 1
 MEAS_F32X4, MEAS_F64X4, MEAS_F32X3 = 0, 1, 2      # include/cpe.h CPE_MEAS_*
 LOSS_REDESCENDING, LOSS_SQUARE = 0, 1             # include/cpe.h CPE_LOSS_*
+STATUS_PIVOT, STATUS_MAXITER, STATUS_NONFINITE = 1, 2, 4      # include/cpe.h CPE_STATUS_* (bit flags; 0 = converged)
 _I32_KEYS = ("chain_link", "eq_pairs", "ineq_idx", "ind_idx", "ind_pos", "grp_ndep", "grp_nnb", "grp_dep", "grp_nb",
              "u_off", "u_item", "col_item", "ent_pq", "a_ptr", "a_items", "e_ptr", "e_items", "i_ptr", "i_items", "diag_ent",
              "grad_ent", "grp_src", "s_src", "s_ptr", "s_items", "ent_order", "s_order", "ent_meta", "a_ell", "e_ell",
@@ -441,10 +442,20 @@ class Solver:
             self.launches += 1
         out = self.evaluate(q, constraints=True)
         res = dict(q=q, cost=out["cost"].clone(), c_eq=out["c_eq"], v_in=out["v_in"], counters=self.counters.clone(),
-                   status=self.status.clone(), lockstep_iterations=total_inner)
+                   status=self.exit_status(out), lockstep_iterations=total_inner)
         if self.priors is not None:
             res["prior_cost"] = out["prior_cost"].clone()
         self.result = res
+
+    def exit_status(self, out):
+        """status[S] of CPE_STATUS_* flags from the final cost, the activity flags of the last round and K3's pivots."""
+        st = torch.zeros(self.b.S, dtype=torch.int32, device=self.cost.device)
+        bs = self.b.struct()
+        _lib.check(self.lib.cpe_finalize_status_f64(C.byref(bs), _ptr(out["cost"]), _ptr(out.get("prior_cost")),
+                                                    _ptr(self.active), _ptr(self.status), _ptr(st), _stream()),
+                   "cpe_finalize_status_f64")
+        self.launches += 1
+        return st
 
 
     # ---- shutter-delay estimation (acinoset_misc.py:182-183, 273-286; SURVEY 8f.4) ------------------------------------
@@ -556,7 +567,7 @@ class Solver:
         self.set_delay(q, tau)
         out = self.evaluate(q, constraints=True)
         self.result = dict(q=q, tau=tau, cost=out["cost"].clone(), c_eq=out["c_eq"], v_in=out["v_in"],
-                           counters=self.counters.clone(), status=self.status.clone(), lockstep_iterations=total_inner)
+                           counters=self.counters.clone(), status=self.exit_status(out), lockstep_iterations=total_inner)
         return self.result
 
 
@@ -642,32 +653,44 @@ class HostEvaluator:
     in waves of `wave` sequences on two streams with two staging sets, so the host->device copy of wave i+1
     overlaps the kernel of wave i.  Per wave it calls `cpe_eval_host_f64` (include/cpe.h): H2D of q and the
     detections, K1 with the chain-sparse Jacobian written to a device buffer, the per-sequence cost reduction,
-    and D2H of cost[S,4]."""
+    and D2H of cost[S,4].  Modes:
+      resident_meas=True  the detections stay on the device (they are constant across the iterations of a solve) and
+                          only q crosses the bus -- what one LM iteration of a host-side caller moves;
+      resid_out=True      the residuals (`meas_err`, the array the reference saves: acinoset_opt.py:318) come back too."""
 
-    def __init__(self, model: Model, proto: Batch, S, wave, jac=True):
+    def __init__(self, model: Model, proto: Batch, S, wave, jac=True, resident_meas=False, resid_out=False):
         self.m, self.lib, self.proto = model, model.lib, proto
         self.S, self.wave, self.N, self.C, self.W = S, wave, proto.N, proto.C, proto.W
+        self.resident_meas, self.resid_out = resident_meas, resid_out
         dev = model.device
         f64 = dict(dtype=torch.float64, device=dev)
         self.streams = [torch.cuda.Stream(device=dev) for _ in range(2)]
         self.stage = []
         for _ in range(2):
             st = dict(q=torch.empty(wave, self.N, 54, **f64),
-                      meas=torch.empty(wave, self.N, self.C, 24, self.W, proto.meas.shape[5], dtype=proto.meas.dtype,
-                                       device=dev),
+                      meas=None if resident_meas else torch.empty(wave, self.N, self.C, 24, self.W, proto.meas.shape[5],
+                                                                  dtype=proto.meas.dtype, device=dev),
                       frame_cost=torch.zeros(wave, self.N, 4, **f64), cost=torch.zeros(wave, 4, **f64),
-                      jac=torch.empty(wave, self.N, self.C, model.jac_width, **f64) if jac else None)
+                      jac=torch.empty(wave, self.N, self.C, model.jac_width, **f64) if jac else None,
+                      resid=torch.empty(wave, self.N, self.C, 24, self.W, 2, **f64) if resid_out else None)
             self.stage.append(st)
         self.h_cost = torch.zeros(S, 4, dtype=torch.float64).pin_memory()
+        self.h_resid = torch.zeros(S, self.N, self.C, 24, self.W, 2, dtype=torch.float64).pin_memory() if resid_out else None
         self.launches = 0
 
     def bytes_per_call(self):
-        h2d = self.S * self.N * (54 * 8 + self.C * 24 * self.W * self.proto.meas.shape[5] * self.proto.meas.element_size())
-        return h2d, self.S * 4 * 8
+        mb = 0 if self.resident_meas else self.C * 24 * self.W * self.proto.meas.shape[5] * self.proto.meas.element_size()
+        h2d = self.S * self.N * (54 * 8 + mb)
+        d2h = self.S * 4 * 8 + (self.S * self.N * self.C * 24 * self.W * 2 * 8 if self.resid_out else 0)
+        return h2d, d2h
 
-    def __call__(self, h_q, h_meas):
-        """h_q[S,N,54] f64 and h_meas[S,N,C,24,W,4|3] pinned host tensors -> pinned cost[S,4] (valid after return)."""
-        assert not h_q.is_cuda and not h_meas.is_cuda and h_q.is_pinned() and h_meas.is_pinned()
+    def __call__(self, h_q, h_meas=None):
+        """h_q[S,N,54] f64 (and, unless resident_meas, h_meas[S,N,C,24,W,4|3]) pinned host tensors -> pinned cost[S,4]
+        (valid after return; `self.h_resid` holds the residuals with resid_out)."""
+        assert not h_q.is_cuda and h_q.is_pinned()
+        assert self.resident_meas == (h_meas is None)
+        if h_meas is not None:
+            assert not h_meas.is_cuda and h_meas.is_pinned()
         cur = torch.cuda.current_stream()
         for st in self.streams:
             st.wait_stream(cur)
@@ -680,10 +703,13 @@ class HostEvaluator:
             eo.frame_cost = stg["frame_cost"].data_ptr()
             if stg["jac"] is not None:
                 eo.jac = stg["jac"].data_ptr()
+            if stg["resid"] is not None:
+                eo.resid = stg["resid"].data_ptr()
             _lib.check(self.lib.cpe_eval_host_f64(
                 C.byref(self.m.struct), C.byref(bs), C.c_void_p(h_q[s0:s1].data_ptr()),
-                C.c_void_p(h_meas[s0:s1].data_ptr()), _ptr(stg["q"]), _ptr(stg["meas"]), C.byref(eo),
-                _ptr(stg["cost"]), C.c_void_p(self.h_cost[s0:s1].data_ptr()), None,
+                None if h_meas is None else C.c_void_p(h_meas[s0:s1].data_ptr()), _ptr(stg["q"]), _ptr(stg["meas"]),
+                C.byref(eo), _ptr(stg["cost"]), C.c_void_p(self.h_cost[s0:s1].data_ptr()),
+                None if self.h_resid is None else C.c_void_p(self.h_resid[s0:s1].data_ptr()),
                 C.c_void_p(stream.cuda_stream)), "cpe_eval_host_f64")
             self.launches += 2
         for st in self.streams:

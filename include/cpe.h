@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 112          /* 0.1.12 */
+#define CPE_VERSION 113          /* 0.1.13 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -65,6 +65,12 @@ extern "C" {
 
 #define CPE_LOSS_REDESCENDING 0  /* acinoset_misc.py:476-482, 2001-2015 */
 #define CPE_LOSS_SQUARE 1        /* hand-labelled data: (w slack)^2, camera multiplier not applied (acinoset_misc.py:471-474) */
+
+/* per-sequence exit status of a solve (bit flags; 0 = converged: the last multiplier round stopped on ftol or at a point
+ * no damping could improve) */
+#define CPE_STATUS_PIVOT 1       /* a block of the banded factorisation had a non-positive pivot */
+#define CPE_STATUS_MAXITER 2     /* the last multiplier round ran out of LM iterations */
+#define CPE_STATUS_NONFINITE 4   /* the final cost is NaN or infinite (NaN in q, the cameras or pre-gated detections) */
 
 #define CPE_E_ARG (-1)
 #define CPE_E_DIM (-2)
@@ -221,7 +227,7 @@ typedef struct cpe_solve_io {
     double *Lfac;                   /* [S,N,3,28,28] workspace: L1, L2, L3 (unit-lower block factors of each block row) */
     double *zbuf;                   /* [S,N,28] workspace */
     double *delta_ind;              /* [S,N,28] out */
-    int32_t *status;                /* [S] out: 0 ok, 1 non-positive pivot encountered */
+    int32_t *status;                /* [S] out: 0 ok, 1 non-positive pivot encountered (CPE_STATUS_PIVOT) */
 } cpe_solve_io;
 
 int cpe_version(void);
@@ -286,12 +292,20 @@ int cpe_band_solve_general_f64(const cpe_batch *batch, const double *Sblk, const
                                int64_t mband_stride, int32_t bw, double *Lband, double *delta_ind, int32_t *status,
                                void *stream);
 
+/* Exit status of a solve, status[S] = CPE_STATUS_* flags: `pivot` = cpe_solve_io.status of the last band solve (may be
+ * NULL), `active` = the LM activity flags when the last round ended (NULL = none), cost[S,4] (+ cost_extra[S,2], may be
+ * NULL) = the final cost terms. */
+int cpe_finalize_status_f64(const cpe_batch *batch, const double *cost, const double *cost_extra, const int32_t *active,
+                            const int32_t *pivot, int32_t *status, void *stream);
+
 /* Augmented-Lagrangian multiplier update: lam_eq += mu_eq * c_eq ; lam_in = mu_in * v_in. */
 int cpe_update_multipliers_f64(const cpe_model *model, const cpe_batch *batch, const double *c_eq,
                                const double *v_in, double *lam_eq, double *lam_in, void *stream);
 
 /* Host-buffer convenience wrapper used for the end-to-end metric: copies q and meas from (pinned) host memory,
- * evaluates, and copies cost[S,4] (and resid if non-NULL) back.  d_* are caller-owned device staging buffers. */
+ * evaluates, and copies cost[S,4] (and resid = the reference's `meas_err`, if h_resid and out_dev->resid are non-NULL)
+ * back.  d_* are caller-owned device staging buffers.  h_meas == NULL: the detections are already resident in
+ * batch_dev->meas (they are constant across the iterations of a solve) and only q crosses the bus. */
 int cpe_eval_host_f64(const cpe_model *model, const cpe_batch *batch_dev, const double *h_q, const void *h_meas,
                       double *d_q, void *d_meas, const cpe_eval_out *out_dev, double *d_cost, double *h_cost,
                       double *h_resid, void *stream);

@@ -541,3 +541,24 @@ def test_shutter_delay_estimation_recovers_delays(gpu):
     c_delay = res["cost"][:, 0:2].sum(dim=1).cpu().numpy()
     assert np.all(c_delay < c_plain), (c_delay, c_plain)
     assert float(res["c_eq"].abs().max()) < 1e-3
+
+
+def test_host_evaluator_modes_match_the_resident_evaluation(gpu):
+    """engine.HostEvaluator (cpe_eval_host_f64, the end-to-end call of bench.py) in its three modes -- all inputs in /
+    detections resident, q only / residuals copied back -- against the device-resident evaluation, over two waves."""
+    import torch
+    from cheetah_pose_estimation_b200 import engine, synthetic
+    prob = synthetic.make_problem(S=5, N=9, C=3, seed=23)
+    batch = prob.to_batch("cuda:0")
+    q = torch.as_tensor(prob.q_init, device="cuda:0")
+    ref = engine.Solver(gpu, batch, with_solver=False).evaluate(q, resid=True, jac=True)     # same kernel flavour (JAC)
+    h_q = q.cpu().pin_memory()
+    h_meas = batch.meas.cpu().pin_memory()
+    for resident, resid_out in ((False, False), (True, False), (False, True)):
+        hev = engine.HostEvaluator(gpu, batch, 5, 3, resident_meas=resident, resid_out=resid_out)
+        cost = hev(h_q, None if resident else h_meas)
+        assert torch.equal(cost, ref["cost"].cpu())
+        h2d, d2h = hev.bytes_per_call()
+        assert h2d == 5 * 9 * 54 * 8 + (0 if resident else h_meas.numel() * h_meas.element_size())
+        if resid_out:
+            assert torch.equal(hev.h_resid, ref["resid"].cpu()) and d2h == 5 * 4 * 8 + ref["resid"].numel() * 8
