@@ -24,8 +24,7 @@ class CpeModel(C.Structure):
         ("ent_pq", c_i32p), ("a_ptr", c_i32p), ("a_items", c_i32p), ("e_ptr", c_i32p), ("e_items", c_i32p),
         ("i_ptr", c_i32p), ("i_items", c_i32p), ("diag_ent", c_i32p), ("grad_ent", c_i32p), ("grp_src", c_i32p),
         ("s_src", c_i32p), ("s_ptr", c_i32p), ("s_items", c_i32p), ("ent_order", c_i32p), ("s_order", c_i32p),
-        ("ent_meta", c_i32p), ("a_ell", c_i32p), ("e_ell", c_i32p), ("i_ell", c_i32p), ("s_meta", c_i32p),
-        ("s_ell", c_i32p),
+        ("k2_tab", C.c_void_p), ("k2_off", C.c_int32 * 48),
     ]
 
 

@@ -7,7 +7,11 @@
 //   acinoset_misc.py:278-288, 459-484, 2001-2015 (measurement), :639-677 (motion), system.py:574-586 (joints),
 //   cheetah.py:306-352 (inequalities).
 //
-// Mapping (sm_100a, FP64): one CTA per frame.  Front end as K1 (sincos -> R -> marker positions, chain derivative
+// Mapping (sm_100a, FP64): PERSISTENT CTAs, one per SM, of NTEAM "frame teams" (5 x 160 threads, or 4 x 192 when a frame has
+// more than 160 (camera, marker) pairs).  The static gather tables (~24 KB, cpe_model.k2_tab) are copied into shared
+// memory ONCE per CTA and shared by its teams; each team walks over frames (team-strided), synchronises on its own named
+// barrier, and fetches the next frame's coordinates and detections into registers while it works on the current one.
+// Per frame: front end as K1 (sincos -> R -> marker positions, chain derivative
 // vectors U).  One thread per (camera, marker) projects, weights by the IRLS curvature max(rho'/E, 0) and leaves a
 // 3x3 + 3 block; blocks are summed over cameras (fixed order) into A_l, b_l.  Every nonzero of the frame Hessian
 // H = sum_l G_l^T A_l G_l (+ mu Jc^T Jc + active inequality rows) and of the gradient is then ONE gather over a
@@ -31,6 +35,8 @@ struct AsmParams {
     cpe_assemble_out ao;
     int TPF;        // C * 24
     int at_size;    // doubles of the aliased region (per-task blocks, then entries + group scratch)
+    int tab_doubles;    // shared-memory doubles taken by the table blob (k2_off[41] / 8, rounded up to 2)
+    int team_doubles;   // shared-memory doubles of one team: cam[C*24] + A_AT + at_size
     double ea, eb, ec, icb;     // exp(loss_a), exp(loss_b), exp(loss_c), 1 / (loss_c - loss_b)
 };
 
@@ -50,37 +56,73 @@ __device__ __forceinline__ double motion_m0(int k, int nf) {
     return s;
 }
 
-template <int MAXT, int MINB>
-__global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_constant__ AsmParams p) {
+template <int TEAM_T>
+__device__ __forceinline__ void team_sync(int team) {
+    asm volatile("bar.sync %0, %1;" ::"r"(team + 1), "n"(TEAM_T) : "memory");
+}
+
+template <int TEAM_T, int NTEAM>
+__global__ void __launch_bounds__(TEAM_T *NTEAM, 1) assemble_kernel(const __grid_constant__ AsmParams p) {
     extern __shared__ __align__(16) double sm[];
-    const int tid = threadIdx.x, nt = blockDim.x;
+    // ---- once per CTA: the gather tables ----------------------------------------------------------------------------------
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(p.m.k2_tab);
+        uint4 *dst = reinterpret_cast<uint4 *>(sm);
+        for (int i = threadIdx.x; i < p.m.k2_off[41] / 16; i += TEAM_T * NTEAM) dst[i] = src[i];
+    }
+    __syncthreads();
+    const unsigned char *tab = reinterpret_cast<const unsigned char *>(sm);
+    const uint2 *t_meta = reinterpret_cast<const uint2 *>(tab + p.m.k2_off[0]);
+    const uint32_t *t_smeta = reinterpret_cast<const uint32_t *>(tab + p.m.k2_off[1]);
+    const int16_t *t_grp = reinterpret_cast<const int16_t *>(tab + p.m.k2_off[2]);
+    const int team = threadIdx.x / TEAM_T, tid = threadIdx.x - team * TEAM_T;
+    constexpr int nt = TEAM_T;
     const int N = p.b.N, C = p.b.C, W = p.b.W, TPF = p.TPF;
-    const int s = blockIdx.x / N, k = blockIdx.x - s * N;      // 1-D grid: S is not bound by the 65535 of grid.y
-    const int nf = p.b.n_frames[s];
-    if (k >= nf || (p.b.active && !p.b.active[s])) return;
-    const size_t fidx = (size_t)s * N + k;
     const int n_ineq = p.m.n_ineq, n_u = p.m.n_u, n_ent = p.m.n_ent;
-    double *cam = sm;
-    double *fr = sm + C * CPE_CAM_STRIDE;
+    double *cam = sm + p.tab_doubles + (size_t)team * p.team_doubles;
+    double *fr = cam + C * CPE_CAM_STRIDE;
     double *GV = fr + A_GV, *BV = fr + A_BV, *AT = fr + A_AT;
     double *ENT = AT, *DDI = AT + ENT_PAD, *YS = DDI + DDI_SZ;
-
     const bool mvalid = tid < TPF;
     const int mc = tid / 24, ml = tid - mc * 24;
+    const long long total = (long long)p.b.S * N, stride = (long long)gridDim.x * NTEAM;
+    long long f = (long long)blockIdx.x * NTEAM + team;
+    // registers of the frame in flight: one coordinate and one detection per thread, fetched one frame ahead
+    double q_pre = 0.0;
+    MeasRaw m_pre;
+    m_pre.d = make_double4(0.0, 0.0, 0.0, 0.0);
+    if (f < total) {
+        if (tid < 54) q_pre = p.q[f * 54 + tid];
+        if (mvalid) meas_fetch(p.b, ((f * C + mc) * 24 + ml) * W, m_pre);
+    }
+    int s_cam = -1;                                      // sequence whose cameras sit in `cam`
+    for (; f < total; f += stride) {
+    const int s = (int)(f / N), k = (int)(f - (long long)s * N);
+    const int nf = p.b.n_frames[s];
+    const double q_cur = q_pre;
+    MeasRaw mraw = m_pre;
+    {
+        const long long f2 = f + stride;                 // next frame of this team: loads in flight during this one
+        if (f2 < total) {
+            if (tid < 54) q_pre = p.q[f2 * 54 + tid];
+            if (mvalid) meas_fetch(p.b, ((f2 * C + mc) * 24 + ml) * W, m_pre);
+        }
+    }
+    if (k >= nf || (p.b.active && !p.b.active[s])) continue;
+    const size_t fidx = (size_t)f;
     const int ncam_s = p.b.n_cams ? p.b.n_cams[s] : C;      // cameras beyond it are padding of a ragged batch (weight 0)
     const size_t midx0 = ((fidx * C + mc) * 24 + ml) * W;
-    MeasRaw mraw;
-    mraw.d = make_double4(0.0, 0.0, 0.0, 0.0);
-    if (mvalid) meas_fetch(p.b, midx0, mraw);
-    const double *qf = p.q + fidx * 54;
-    for (int c = tid; c < 54; c += nt) fr[A_QO + c] = qf[c];
-    for (int i = tid; i < C * CPE_CAM_STRIDE; i += nt) cam[i] = p.b.cams[(size_t)s * C * CPE_CAM_STRIDE + i];
+    if (tid < 54) fr[A_QO + tid] = q_cur;
+    if (s != s_cam) {                                    // consecutive frames of a team mostly share the sequence
+        for (int i = tid; i < C * CPE_CAM_STRIDE; i += nt) cam[i] = p.b.cams[(size_t)s * C * CPE_CAM_STRIDE + i];
+        s_cam = s;
+    }
     if (tid < 10) GV[tid] = (tid == 0 || tid == 4 || tid == 8) ? 1.0 : 0.0;      // identity columns e_x, e_y, e_z
-    __syncthreads();
+    team_sync<TEAM_T>(team);
     for (int a = tid; a < 51; a += nt) sincos(fr[A_QO + 3 + a], &fr[A_SCO + 2 * a], &fr[A_SCO + 2 * a + 1]);
-    __syncthreads();
+    team_sync<TEAM_T>(team);
     for (int link = tid; link < 17; link += nt) rot_from_sc(fr + A_SCO + 6 * link, fr + A_RO + 9 * link);
-    __syncthreads();
+    team_sync<TEAM_T>(team);
 
     // ---- camera-independent items: positions, U, joint rows, inequality rows, motion gradient --------------------
     const double h = p.b.h[s];
@@ -174,7 +216,7 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
             }
         }
     }
-    __syncthreads();
+    team_sync<TEAM_T>(team);
 
     // ---- one thread per (camera, marker): projection + IRLS-weighted 3x3 block and gradient 3-vector -------------
     if (mvalid) {
@@ -224,7 +266,7 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
         ab[7] = gu * pr.du[1] + gv * pr.dv[1];
         ab[8] = gu * pr.du[2] + gv * pr.dv[2];
     }
-    __syncthreads();
+    team_sync<TEAM_T>(team);
     if (p.ao.cam_blocks) {
         // per camera: sum over markers of the point-space curvature (6) and gradient (3) -- what the shutter-delay
         // unknowns see (d slack / d tau_c and the cross-frame base terms are d(u,v)/d(point) times a 3-vector)
@@ -249,7 +291,7 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
             BV[9 * l + 3 * ri + ci] = v;
         }
     }
-    __syncthreads();
+    team_sync<TEAM_T>(team);
     // ---- B = A_l U for every chain column ------------------------------------------------------------------------------
     for (int it = tid; it < n_u; it += nt) {
         const int l = p.m.u_item[it] >> 8;
@@ -260,34 +302,32 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
         BV[B_U0 + o + 1] = Al[1] * u0 + Al[4] * u1 + Al[7] * u2;
         BV[B_U0 + o + 2] = Al[2] * u0 + Al[5] * u1 + Al[8] * u2;
     }
-    __syncthreads();
+    team_sync<TEAM_T>(team);
     // ---- every Hessian / gradient nonzero = one gather over its static item list -------------------------------------
-    // slot-major tables (skeleton.ell_tables): lane <-> consecutive eo, so every table load of a warp is one line and
-    // no load address depends on a loaded index
+    // slot-major tables in shared memory (skeleton.k2_tables): lane <-> consecutive eo, no bank conflicts, no address
+    // that depends on a loaded index
     {
-        const uint2 *meta = reinterpret_cast<const uint2 *>(p.m.ent_meta);
-        const int32_t *a_ell = p.m.a_ell, *e_ell = p.m.e_ell, *i_ell = p.m.i_ell;
         for (int eo = tid; eo < n_ent; eo += nt) {
-            const uint2 m = meta[eo];
+            const uint2 m = t_meta[eo];
             const int e = m.x & 1023, pp = (m.x >> 10) & 63, qq = (m.x >> 16) & 63;
             const int na = m.y & 255, ne = (m.y >> 8) & 255, ni = m.y >> 16;
             const bool grad = qq == GRAD_Q;
             double acc = 0.0;
 #pragma unroll 4
             for (int i = 0; i < na; ++i) {
-                const int it = a_ell[i * CPE_ELL_ENT + eo];
+                const int it = reinterpret_cast<const int32_t *>(tab + p.m.k2_off[3 + i])[eo];
                 const double *g = GV + (it >> 16), *b = BV + (it & 0xFFFF);
                 acc += g[0] * b[0] + g[1] * b[1] + g[2] * b[2];
             }
             double acce = 0.0;
             for (int i = 0; i < ne; ++i) {
-                const int it = e_ell[i * CPE_ELL_ENT + eo];
+                const int it = reinterpret_cast<const uint16_t *>(tab + p.m.k2_off[27 + i])[eo];
                 const double gi = fr[A_EQG + (it >> 8)];
                 acce += gi * (grad ? fr[A_EQR + (it & 255)] : mu_eq * fr[A_EQG + (it & 255)]);
             }
             double acci = 0.0;
             for (int i = 0; i < ni; ++i) {
-                const int it = i_ell[i * CPE_ELL_ENT + eo];
+                const int it = (tab + p.m.k2_off[32 + i])[eo];
                 const double v = fr[A_VIN + (it >> 1)];
                 const double val = grad ? v : (v != 0.0 ? 1.0 : 0.0);
                 acci += (it & 1) ? -val : val;
@@ -304,15 +344,15 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
             ENT[e] = acc;
         }
     }
-    __syncthreads();
+    team_sync<TEAM_T>(team);
     const double h4 = h * h * h * h;
     if (tid < 54) {
         const double d = ENT[p.m.diag_ent[tid]] + motion_m0(k, nf) * 2.0 * p.m.wq[tid] / h4;
         fr[A_DIAG + tid] = d;
         if (p.ao.diagH) p.ao.diagH[fidx * 54 + tid] = d;
     }
-    if (!p.ao.S) return;
-    __syncthreads();
+    if (!p.ao.S) { team_sync<TEAM_T>(team); continue; }
+    team_sync<TEAM_T>(team);
 
     // ---- per-frame elimination of the dependent coordinates: one warp per group, tableau column per lane ----------
     const double damp = p.damp[s];
@@ -321,7 +361,7 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
     const int n_groups = p.m.n_groups;
     for (int g = wid; g < n_groups; g += nw) {
         double t[GD];
-        const int32_t *src = p.m.grp_src + g * GD * TW;
+        const int16_t *src = t_grp + g * GD * TW;
 #pragma unroll
         for (int i = 0; i < GD; ++i) {
             double v = 0.0;
@@ -356,18 +396,16 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
             }
         }
     }
-    __syncthreads();
+    team_sync<TEAM_T>(team);
     // ---- reduced block S = H_ii + damping - sum_g Hdi^T Y and ghat = g_i - sum_g Hdi^T y (static gather) ----------------
     double *So = p.ao.S + fidx * 784;
-    const uint32_t *s_meta = p.m.s_meta;
-    const int32_t *s_ell = p.m.s_ell;
     for (int eo = tid; eo < 28 * 29; eo += nt) {
-        const uint32_t m = s_meta[eo];
+        const uint32_t m = t_smeta[eo];
         const int r = m & 31, c = (m >> 5) & 31, ns = (m >> 10) & 7, si = m >> 13;
         double v = si != 1023 ? ENT[si] : 0.0;
         if (r == c) v += damp * fr[A_DIAG + p.m.ind_idx[r]];
         for (int i = 0; i < ns; ++i) {
-            const int it = s_ell[i * CPE_ELL_S + eo];
+            const int it = reinterpret_cast<const uint16_t *>(tab + p.m.k2_off[36 + i])[eo];
             const int g = it >> 8, a = (it >> 4) & 15, b = it & 15;
             const double *D = DDI + g * GD * GN + a;
             const double *Yc = YS + g * GD * (GN + 1) + (b == 15 ? GN : b);
@@ -379,18 +417,22 @@ __global__ void __launch_bounds__(MAXT, MINB) assemble_kernel(const __grid_const
         if (c == 28) p.ao.ghat[fidx * 28 + r] = v;
         else So[r * 28 + c] = v;
     }
+    team_sync<TEAM_T>(team);       // the next frame overwrites this team's scratch
+    }   // frames of this team
 }
 
-template <int MAXT, int MINB>
-static int launch_asm(const AsmParams &p, dim3 grid, int threads, size_t smem, cudaStream_t st) {
-    cudaError_t e = cudaFuncSetAttribute(assemble_kernel<MAXT, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+template <int TEAM_T, int NTEAM>
+static int launch_asm(const AsmParams &p, size_t smem, cudaStream_t st) {
+    cudaError_t e = cudaFuncSetAttribute(assemble_kernel<TEAM_T, NTEAM>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)smem);
     if (e != cudaSuccess) return (int)e;
-    // all of the L1/shared array as shared memory: the default carve-out stops at 5 CTAs of 31 KB
-    e = cudaFuncSetAttribute(assemble_kernel<MAXT, MINB>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                             cudaSharedmemCarveoutMaxShared);
-    if (e != cudaSuccess) return (int)e;
-    assemble_kernel<MAXT, MINB><<<grid, threads, smem, st>>>(p);
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const long long frames = (long long)p.b.S * p.b.N;
+    long long grid = (frames + NTEAM - 1) / NTEAM;
+    if (grid > sms) grid = sms;                      // persistent: one CTA per SM, its teams stride over the frames
+    assemble_kernel<TEAM_T, NTEAM><<<(unsigned)grid, TEAM_T * NTEAM, smem, st>>>(p);
     return (int)cudaGetLastError();
 }
 
@@ -404,9 +446,7 @@ extern "C" int cpe_assemble_f64(const cpe_model *model, const cpe_batch *b, cons
     if ((long long)b->S * b->N > 2147483647LL || model->n_ineq > CPE_MAX_INEQ || model->n_groups > CPE_MAX_GROUPS)
         return CPE_E_DIM;
     if (model->n_u != 198 || model->n_ent <= 0 || model->n_ent > ENT_PAD) return CPE_E_DIM;
-    if (!model->ent_meta || !model->a_ell || !model->e_ell || !model->i_ell || !model->s_meta || !model->s_ell ||
-        !model->diag_ent || !model->grp_src || !model->grp_dep || !model->ind_idx)
-        return CPE_E_NULL;
+    if (!model->k2_tab || !model->diag_ent || !model->grp_dep || !model->ind_idx) return CPE_E_NULL;
     if (out->S && (!damp || !out->ghat || !out->Y || !out->y)) return CPE_E_NULL;
     if ((b->shutter_tau || b->base_dq || b->base_ddq) && !(b->shutter_tau && b->base_dq && b->base_ddq)) return CPE_E_NULL;
     AsmParams p;
@@ -416,10 +456,13 @@ extern "C" int cpe_assemble_f64(const cpe_model *model, const cpe_batch *b, cons
     p.icb = 1.0 / (b->loss_c - b->loss_b);
     const int need = ENT_PAD + DDI_SZ + YS_SZ;
     p.at_size = p.TPF * 9 > need ? p.TPF * 9 : need;
-    const size_t smem = (size_t)(b->C * CPE_CAM_STRIDE + A_AT + p.at_size) * sizeof(double);
-    int threads = ((p.TPF + 31) / 32) * 32;
-    if (threads < 160) threads = 160;               // >= 5 warps: one per elimination group
-    const dim3 grid((unsigned)(b->N * b->S), 1, 1);
-    if (threads <= 160) return launch_asm<160, 6>(p, grid, threads, smem, (cudaStream_t)stream);
-    return launch_asm<192, 4>(p, grid, threads, smem, (cudaStream_t)stream);
+    p.team_doubles = (b->C * CPE_CAM_STRIDE + A_AT + p.at_size + 1) & ~1;
+    p.tab_doubles = ((model->k2_off[41] + 15) / 16) * 2;
+    if (model->k2_off[41] <= 0 || model->k2_off[41] % 16) return CPE_E_DIM;
+    if (p.TPF <= 160) {
+        const size_t smem = (size_t)(p.tab_doubles + 5 * p.team_doubles) * sizeof(double);
+        return launch_asm<160, 5>(p, smem, (cudaStream_t)stream);
+    }
+    const size_t smem = (size_t)(p.tab_doubles + 4 * p.team_doubles) * sizeof(double);
+    return launch_asm<192, 4>(p, smem, (cudaStream_t)stream);
 }

@@ -471,50 +471,79 @@ def assemble_tables(t=None, kinetic_dataset=False):
                i_ptr=i_ptr, i_items=i_items, diag_ent=diag_ent, grad_ent=grad_ent, grp_src=grp_src.reshape(-1),
                s_src=s_src.reshape(-1), s_ptr=s_ptr, s_items=np.array(s_items, np.int32), ent_order=ent_order,
                s_order=s_order)
-    out.update(ell_tables(out, t["ind_idx"]))
+    out.update(k2_tables(out, t["ind_idx"]))
     return out
 
 
-ELL_ENT, ELL_S = 640, 832           # row strides of the slot-major tables (include/cpe.h CPE_ELL_*)
-ELL_A_SLOTS, ELL_E_SLOTS, ELL_I_SLOTS, ELL_S_SLOTS = 24, 5, 4, 5
+K2_ENT_PAD = 640            # >= n_ent, multiple of 32 (include/cpe.h CPE_K2_ENT_PAD)
+K2_S_PAD = 832              # >= 28 * 29
+K2_MAX_A, K2_MAX_E, K2_MAX_I, K2_MAX_S = 24, 5, 4, 5
+K2_OFF_META, K2_OFF_SMETA, K2_OFF_GRP, K2_OFF_A, K2_OFF_E, K2_OFF_I, K2_OFF_S, K2_OFF_END = 0, 1, 2, 3, 27, 32, 36, 41
 
 
-def ell_tables(a, ind_idx):
-    """The same gather lists in the layout K2 reads: one packed word per work item IN PROCESSING ORDER and the list
-    items slot-major (`a_ell[slot * ELL_ENT + eo]`), so that the 32 lanes of a warp, which work on consecutive `eo`,
-    load consecutive words and no load address depends on a previously loaded index (the CSR form costs three dependent
-    global loads per entry: order -> pointer -> item).  The order of the items inside a list is unchanged, hence every
-    sum is bit-identical to the CSR walk.
-        ent_meta[eo] = (e | p << 10 | q << 16,  n_a | n_e << 8 | n_i << 16)
-        s_meta[eo]   = r | c << 5 | n_s << 10 | src << 13     (src = entry holding H(ind_r, ind_c) or g(ind_r); 1023 = none)"""
+def k2_tables(a, ind_idx):
+    """The gather lists of K2 as ONE byte blob that every CTA copies into shared memory once (`cpe_model.k2_tab`), plus
+    the byte offsets of its sections (`cpe_model.k2_off`).  Work items are stored IN PROCESSING ORDER (eo = position in
+    `ent_order` / `s_order`), one packed word per item and the list items slot-major -- `slot[i][eo]` = i-th item of work
+    item eo -- so the 32 lanes of a warp, which work on consecutive eo, read consecutive words (no bank conflicts) and
+    no address depends on a loaded index.  Because both orders put the longest lists first, slot i is only ever read
+    for a prefix of the work items: each slot is stored up to that prefix (rounded to 32), which keeps the blob at
+    ~24 KB instead of the 130 KB of full-width tables.  Item order inside a list is unchanged: every sum is
+    bit-identical to a walk of the CSR tables, which remain the definition (tests/test_assemble_tables.py).
+        meta[eo]   uint2  { e | p << 10 | q << 16 ,  n_a | n_e << 8 | n_i << 16 }
+        a slots    int32  (offset in G space << 16) | offset in B space
+        e slots    uint16 (eqg index << 8) | (eqg index | eq row)        i slots  uint8  (row << 1) | negative
+        smeta[eo]  uint32 r | c << 5 | n_s << 10 | src << 13   (src = entry of H(ind_r, ind_c) or g(ind_r); 1023 = none)
+        s slots    uint16 (group << 8) | (a << 4) | b                     grp      int16  tableau sources"""
     n_ent = int(a["n_ent"])
-    assert n_ent <= ELL_ENT and n_ent < 1024
-    ent_meta = np.zeros((ELL_ENT, 2), np.uint32)
-    a_ell = np.zeros((ELL_A_SLOTS, ELL_ENT), np.int32)
-    e_ell = np.zeros((ELL_E_SLOTS, ELL_ENT), np.int32)
-    i_ell = np.zeros((ELL_I_SLOTS, ELL_ENT), np.int32)
+    assert n_ent <= K2_ENT_PAD and n_ent < 1024
+
+    def lists(order, ptr, items):
+        return [list(items[int(ptr[int(e)]):int(ptr[int(e) + 1])]) for e in order]
+
+    def slots(ls, cap, dtype, pad):
+        """Per slot i: array of width roundup32(1 + last eo with len > i) holding item i of every work item."""
+        out = []
+        assert max(len(l) for l in ls) <= cap
+        for i in range(cap):
+            has = [eo for eo, l in enumerate(ls) if len(l) > i]
+            width = min(pad, ((has[-1] + 1 + 31) // 32) * 32) if has else 0
+            arr = np.zeros(width, dtype)
+            for eo in has:
+                assert 0 <= ls[eo][i] <= np.iinfo(dtype).max
+                arr[eo] = ls[eo][i]
+            out.append(arr)
+        return out
+
+    la = lists(a["ent_order"], a["a_ptr"], a["a_items"])
+    le = lists(a["ent_order"], a["e_ptr"], a["e_items"])
+    li = lists(a["ent_order"], a["i_ptr"], a["i_items"])
+    ls_ = lists(a["s_order"], a["s_ptr"], a["s_items"])
+    meta = np.zeros((K2_ENT_PAD, 2), np.uint32)
     for eo, e in enumerate(a["ent_order"]):
-        e = int(e)
-        pq = int(a["ent_pq"][e])
-        lists = []
-        for ptr, items, ell, cap in ((a["a_ptr"], a["a_items"], a_ell, ELL_A_SLOTS), (a["e_ptr"], a["e_items"], e_ell, ELL_E_SLOTS),
-                                     (a["i_ptr"], a["i_items"], i_ell, ELL_I_SLOTS)):
-            lst = items[int(ptr[e]):int(ptr[e + 1])]
-            assert len(lst) <= cap
-            ell[:len(lst), eo] = lst
-            lists.append(len(lst))
-        ent_meta[eo] = (e | ((pq >> 6) << 10) | ((pq & 63) << 16), lists[0] | (lists[1] << 8) | (lists[2] << 16))
-    n_s = N_IND * (N_IND + 1)
-    assert n_s <= ELL_S
-    s_meta = np.zeros(ELL_S, np.uint32)
-    s_ell = np.zeros((ELL_S_SLOTS, ELL_S), np.int32)
+        pq = int(a["ent_pq"][int(e)])
+        meta[eo] = (int(e) | ((pq >> 6) << 10) | ((pq & 63) << 16), len(la[eo]) | (len(le[eo]) << 8) | (len(li[eo]) << 16))
+    smeta = np.zeros(K2_S_PAD, np.uint32)
     for eo, e in enumerate(a["s_order"]):
-        e = int(e)
-        r, c = divmod(e, N_IND + 1)
-        lst = a["s_items"][int(a["s_ptr"][e]):int(a["s_ptr"][e + 1])]
-        assert len(lst) <= ELL_S_SLOTS
-        s_ell[:len(lst), eo] = lst
+        r, c = divmod(int(e), N_IND + 1)
         src = int(a["grad_ent"][int(ind_idx[r])]) if c == N_IND else int(a["s_src"][r * N_IND + c])
-        s_meta[eo] = r | (c << 5) | (len(lst) << 10) | ((src if src >= 0 else 1023) << 13)
-    return dict(ent_meta=ent_meta.view(np.int32).reshape(-1), a_ell=a_ell.reshape(-1), e_ell=e_ell.reshape(-1),
-                i_ell=i_ell.reshape(-1), s_meta=s_meta.view(np.int32), s_ell=s_ell.reshape(-1))
+        smeta[eo] = r | (c << 5) | (len(ls_[eo]) << 10) | ((src if src >= 0 else 1023) << 13)
+    grp = np.zeros(((len(a["grp_src"]) + 7) // 8) * 8, np.int16)
+    grp[:len(a["grp_src"])] = a["grp_src"]
+    sections = [meta.view(np.uint8).reshape(-1), smeta.view(np.uint8), grp.view(np.uint8)]
+    sections += [x.view(np.uint8) for x in slots(la, K2_MAX_A, np.int32, K2_ENT_PAD)]
+    sections += [x.view(np.uint8) for x in slots(le, K2_MAX_E, np.uint16, K2_ENT_PAD)]
+    sections += [x.view(np.uint8) for x in slots(li, K2_MAX_I, np.uint8, K2_ENT_PAD)]
+    sections += [x.view(np.uint8) for x in slots(ls_, K2_MAX_S, np.uint16, K2_S_PAD)]
+    assert len(sections) == K2_OFF_END
+    off, blob = [], []
+    pos = 0
+    for sec in sections:
+        off.append(pos)
+        pad = (-len(sec)) % 16
+        blob.append(np.concatenate([sec, np.zeros(pad, np.uint8)]))
+        pos += len(sec) + pad
+    off.append(pos)
+    k2_off = np.zeros(48, np.int32)
+    k2_off[:len(off)] = off
+    return dict(k2_tab=np.concatenate(blob), k2_off=k2_off)

@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 113          /* 0.1.13 */
+#define CPE_VERSION 114          /* 0.1.14 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -51,8 +51,8 @@ extern "C" {
 #define CPE_GRP_MAX_NB 12        /* ... coupled to <= 12 independent coords */
 #define CPE_MAX_GROUPS 8
 #define CPE_COST_TERMS 4         /* measurement, model, al_eq, al_in */
-#define CPE_ELL_ENT 640          /* row stride of cpe_model.a_ell / e_ell / i_ell (>= n_ent) */
-#define CPE_ELL_S 832            /* row stride of cpe_model.s_ell (>= 28 * 29) */
+#define CPE_K2_ENT_PAD 640       /* work items of K2's entry gather, padded (>= n_ent) */
+#define CPE_K2_S_PAD 832         /* work items of K2's Schur gather, padded (>= 28 * 29) */
 
 #define CPE_CAM_FISHEYE 0        /* acinoset_misc.py:1663-1679 */
 #define CPE_CAM_PINHOLE 1        /* acinoset_misc.py:1682-1696 */
@@ -115,15 +115,14 @@ typedef struct cpe_model {
     const int32_t *s_items;
     const int32_t *ent_order;       /* [n_ent] processing order of the entries, longest gather list first */
     const int32_t *s_order;         /* [28*29] processing order of the Schur items, longest list first */
-    /* The same lists in the layout K2 reads (skeleton.ell_tables): one packed word per work item in processing order,
-       list items slot-major, so consecutive lanes load consecutive words and no address depends on a loaded index.
-       The CSR tables above remain the definition (tests/test_assemble_tables.py checks both against each other). */
-    const uint32_t *ent_meta;       /* [CPE_ELL_ENT][2] { e | p << 10 | q << 16,  n_a | n_e << 8 | n_i << 16 } */
-    const int32_t *a_ell;           /* [24][CPE_ELL_ENT] */
-    const int32_t *e_ell;           /* [5][CPE_ELL_ENT] */
-    const int32_t *i_ell;           /* [4][CPE_ELL_ENT] */
-    const uint32_t *s_meta;         /* [CPE_ELL_S] r | c << 5 | n_s << 10 | src << 13 (src 1023 = structural zero) */
-    const int32_t *s_ell;           /* [5][CPE_ELL_S] */
+    /* The same lists as ONE blob in the layout K2 copies to shared memory once per CTA (skeleton.k2_tables): work items in
+       processing order, list items slot-major, each slot truncated to the prefix of work items that reach it.  The CSR
+       tables above remain the definition (tests/test_assemble_tables.py checks the blob against them).
+       k2_off[] = byte offsets of the sections: [0] meta uint2[CPE_K2_ENT_PAD], [1] smeta uint32[CPE_K2_S_PAD],
+       [2] grp int16, [3..26] a slots int32, [27..31] e slots uint16, [32..35] i slots uint8, [36..40] s slots uint16,
+       [41] total bytes (multiple of 16). */
+    const void *k2_tab;
+    int32_t k2_off[48];
 } cpe_model;
 
 /* One batch of sequences. */

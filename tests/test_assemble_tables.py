@@ -123,25 +123,35 @@ def test_tables_reproduce_oracle_normal_equations():
     assert np.abs(ghat - ghat_ref).max() <= 1e-9 * np.abs(ghat_ref).max()
 
 
-def test_ell_tables_hold_the_same_lists_in_processing_order():
-    """skeleton.ell_tables (the slot-major layout K2 reads) against the CSR definition: same entries, same items in the
-    same order, processing order = ent_order / s_order."""
+def test_k2_table_blob_holds_the_same_lists_in_processing_order():
+    """skeleton.k2_tables (the blob K2 copies to shared memory) against the CSR definition: same entries, same items in
+    the same order, processing order = ent_order / s_order, every slot wide enough for the work items that reach it."""
     t = sk.build_tables(False)
     at = sk.assemble_tables(t)
-    meta = at["ent_meta"].view(np.uint32).reshape(-1, 2)
-    for name, slots, ptr, items in (("a_ell", sk.ELL_A_SLOTS, "a_ptr", "a_items"), ("e_ell", sk.ELL_E_SLOTS, "e_ptr", "e_items"),
-                                    ("i_ell", sk.ELL_I_SLOTS, "i_ptr", "i_items")):
-        ell = at[name].reshape(slots, sk.ELL_ENT)
-        shift = {"a_ell": 0, "e_ell": 8, "i_ell": 16}[name]
+    blob, off = at["k2_tab"], at["k2_off"]
+    assert blob.dtype == np.uint8 and len(blob) == off[sk.K2_OFF_END] and len(blob) % 16 == 0 and len(blob) < 32768
+    assert all(int(o) % 16 == 0 for o in off[:sk.K2_OFF_END + 1])
+
+    def sec(i, dtype):
+        return blob[int(off[i]):int(off[i + 1])].view(dtype)
+
+    meta = sec(sk.K2_OFF_META, np.uint32).reshape(-1, 2)
+    assert meta.shape[0] == sk.K2_ENT_PAD
+    for base, cap, ptr, items, dtype, shift in ((sk.K2_OFF_A, sk.K2_MAX_A, "a_ptr", "a_items", np.int32, 0),
+                                                (sk.K2_OFF_E, sk.K2_MAX_E, "e_ptr", "e_items", np.uint16, 8),
+                                                (sk.K2_OFF_I, sk.K2_MAX_I, "i_ptr", "i_items", np.uint8, 16)):
+        slots = [sec(base + i, dtype) for i in range(cap)]
         for eo, e in enumerate(at["ent_order"]):
             e = int(e)
             assert int(meta[eo, 0] & 1023) == e
             assert int((meta[eo, 0] >> 10) & 63) * 64 + int((meta[eo, 0] >> 16) & 63) == int(at["ent_pq"][e])
             n = int((meta[eo, 1] >> shift) & 255)
             lst = at[items][int(at[ptr][e]):int(at[ptr][e + 1])]
-            assert n == len(lst) and np.array_equal(ell[:n, eo], lst)
-    sm = at["s_meta"].view(np.uint32)
-    s_ell = at["s_ell"].reshape(sk.ELL_S_SLOTS, sk.ELL_S)
+            assert n == len(lst)
+            for i in range(n):
+                assert eo < len(slots[i]) and int(slots[i][eo]) == int(lst[i])
+    sm = sec(sk.K2_OFF_SMETA, np.uint32)
+    s_slots = [sec(sk.K2_OFF_S + i, np.uint16) for i in range(sk.K2_MAX_S)]
     for eo, e in enumerate(at["s_order"]):
         e = int(e)
         r, c = divmod(e, 29)
@@ -149,6 +159,10 @@ def test_ell_tables_hold_the_same_lists_in_processing_order():
         assert (m & 31, (m >> 5) & 31) == (r, c)
         lst = at["s_items"][int(at["s_ptr"][e]):int(at["s_ptr"][e + 1])]
         n = (m >> 10) & 7
-        assert n == len(lst) and np.array_equal(s_ell[:n, eo], lst)
+        assert n == len(lst)
+        for i in range(n):
+            assert eo < len(s_slots[i]) and int(s_slots[i][eo]) == int(lst[i])
         src = int(at["grad_ent"][int(t["ind_idx"][r])]) if c == 28 else int(at["s_src"][r * 28 + c])
         assert (m >> 13) == (src if src >= 0 else 1023)
+    grp = sec(sk.K2_OFF_GRP, np.int16)
+    assert np.array_equal(grp[:len(at["grp_src"])], at["grp_src"])
