@@ -48,6 +48,31 @@ __device__ __forceinline__ void dmma(double &c0, double &c1, double a, double b)
 
 __device__ __forceinline__ void bar_math() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
+// ---- mbarrier + 1-D bulk async copy (global -> shared), used by the backward substitution ----------------------------------
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *b, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long *b) {
+    asm volatile("{ .reg .b64 t; mbarrier.arrive.shared::cta.b64 t, [%0]; }" ::"r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *b, unsigned bytes) {
+    asm volatile("{ .reg .b64 t; mbarrier.arrive.expect_tx.shared::cta.b64 t, [%0], %1; }" ::"r"(smem_u32(b)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *b, unsigned parity) {
+    asm volatile(
+        "{ .reg .pred p;\n"
+        "W: mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@!p bra W; }" ::"r"(smem_u32(b)), "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned bytes, unsigned long long *b) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(b))
+                 : "memory");
+}
+
 // acc (rows 8w..8w+7, all 32 padded columns) += sgn * X[rows] . Y^T ; X, Y row-major 28x28 in shared memory.
 // Lane (gr, gc): A fragment X[r][4ks+gc], B fragment Y[8t+gr][4ks+gc]; padded rows/columns contribute zeros.
 template <bool NEG>
@@ -336,14 +361,49 @@ __global__ void __launch_bounds__(SOLVE_THREADS, 3) band_solve_kernel(const __gr
         }
     }
     // ---- backward: d_k = u_k - L1(k+1)^T d_{k+1} - L2(k+2)^T d_{k+2} - L3(k+3)^T d_{k+3} ----------------------------
+    // The factor blocks come back from HBM through the (now dead) operand window: three stages of three 28x28 blocks,
+    // filled two rows ahead by bulk async copies (cp.async.bulk -> mbarrier complete_tx), so the 500 dependent steps of
+    // a sequence no longer wait for a DRAM round trip each.
     double *dout = p.io.delta_ind + (size_t)s * N * NB;
+    __shared__ __align__(8) unsigned long long mbar[3];
+    // every thread's factor stores (global) and window stores (shared) went through the generic proxy: order them before
+    // the async-proxy copies that follow
+    asm volatile("fence.proxy.async;" ::: "memory");
+    if (tid == 0) {
+        for (int i = 0; i < 3; ++i) mbar_init(&mbar[i], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    auto issue = [&](int kq) {                            // thread 0: blocks needed by step kq into stage kq % 3
+        const int st = kq % 3;
+        int nv = 0;
+        for (int j = 0; j < 3; ++j) nv += (kq + j + 1 < nf) ? 1 : 0;
+        if (nv == 0) { mbar_arrive(&mbar[st]); return; }
+        mbar_expect_tx(&mbar[st], (unsigned)(nv * BLK * sizeof(double)));
+        for (int j = 0; j < 3; ++j) {
+            const int kk = kq + j + 1;
+            if (kk < nf) bulk_g2s(sm + (st * 3 + j) * BLK, Lf + ((size_t)kk * 3 + j) * BLK, (unsigned)(BLK * sizeof(double)), &mbar[st]);
+        }
+    };
+    if (tid == 0) {
+        if (nf >= 1) issue(nf - 1);
+        if (nf >= 2) issue(nf - 2);
+    }
+    unsigned phase = 0;                                   // bit st = parity the next wait on stage st expects
+    double z_next = (tid < NB && nf >= 1) ? zb[(size_t)(nf - 1) * NB + tid] : 0.0;
     for (int k = nf - 1; k >= 0; --k) {
+        const int st = k % 3;
+        const double z_cur = z_next;
+        if (tid < NB && k >= 1) z_next = zb[(size_t)(k - 1) * NB + tid];
+        if (tid == 0 && k >= 2) issue(k - 2);             // stage (k + 1) % 3: its readers passed the barrier ending step k + 1
+        mbar_wait(&mbar[st], (phase >> st) & 1u);
+        phase ^= 1u << st;
         if (tid < 84) {
             const int j = tid / NB, c = tid - j * NB;     // block offset j+1
             const int kk = k + j + 1;
             double acc = 0.0;
             if (kk < nf) {
-                const double *Lb = Lf + ((size_t)kk * 3 + j) * BLK + c;
+                const double *Lb = sm + (st * 3 + j) * BLK + c;
                 const double *dk = dv + (kk & 3) * NB;
                 double a0 = 0.0, a1 = 0.0;
 #pragma unroll
@@ -357,7 +417,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS, 3) band_solve_kernel(const __gr
         }
         __syncthreads();
         if (tid < NB) {
-            const double d = zb[(size_t)k * NB + tid] - part[tid] - part[NB + tid] - part[2 * NB + tid];
+            const double d = z_cur - part[tid] - part[NB + tid] - part[2 * NB + tid];
             dv[(k & 3) * NB + tid] = d;
             dout[(size_t)k * NB + tid] = d;
         }
