@@ -41,8 +41,10 @@ struct AsmParams {
 };
 
 // per-frame shared layout (doubles), after cam[C*24]
-constexpr int A_QO = 0, A_SCO = 56, A_RO = 160, A_POSO = 314, A_GV = 386, A_BV = 1056, A_EQG = 2004, A_EQR = 2160,
-              A_VIN = 2186, A_MOG = 2218, A_DIAG = 2272, A_AT = 2326;
+// sin/cos and the link rotations are dead once the per-frame items are done, i.e. before the first write to the aliased
+// region AT (per-pair blocks, then entries + elimination scratch): they live at its start.
+constexpr int A_QO = 0, A_POSO = 56, A_GV = 128, A_BV = 798, A_EQG = 1746, A_EQR = 1902, A_VIN = 1928, A_MOG = 1960,
+              A_DIAG = 2014, A_AT = 2068, A_SCO = A_AT, A_RO = A_AT + 104;
 constexpr int G_U0 = 10, B_U0 = 216, B_G0 = 876, GRAD_Q = 63;       // must match skeleton.py
 constexpr int ENT_PAD = 640, DDI_SZ = CPE_MAX_GROUPS * 72, YS_SZ = CPE_MAX_GROUPS * 78;
 
@@ -460,6 +462,8 @@ extern "C" int cpe_assemble_f64(const cpe_model *model, const cpe_batch *b, cons
     p.tab_doubles = ((model->k2_off[41] + 15) / 16) * 2;
     if (model->k2_off[41] <= 0 || model->k2_off[41] % 16) return CPE_E_DIM;
     if (p.TPF <= 160) {
+        // five teams: 25 warps at 72 registers.  Measured at 1776 x 500 (profiles/r2i_k2_teams.txt): 6 teams / 64 registers
+        // 31.2 ms, 5 / 72: 29.3 ms, 4 / 96: 30.0 ms, 3 / 128: 32.9 ms
         const size_t smem = (size_t)(p.tab_doubles + 5 * p.team_doubles) * sizeof(double);
         return launch_asm<160, 5>(p, smem, (cudaStream_t)stream);
     }
