@@ -60,6 +60,8 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-f32", action="store_true", help="skip the FP32-flavour leg")
     ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--unique", type=int, default=4096,
+                    help="distinct trajectories / camera rings generated per rank (SURVEY 8d: one per sequence)")
     return ap.parse_args()
 
 
@@ -232,7 +234,7 @@ def run_b200(a):
     wave = min(a.wave, S)
     model = engine.Model(dev)
     batch, q_true, q_init = synthetic.make_device_problem(S, N, C, seed=a.seed + 1000 * rank, device=dev,
-                                                          dlc_native=True)
+                                                          dlc_native=True, n_unique=a.unique)
     gen = torch.Generator(device=dev)
     gen.manual_seed(a.seed + 100 + rank)
     q = (q_true + 0.05 * torch.randn(q_true.shape, generator=gen, device=dev, dtype=torch.float64)).contiguous()

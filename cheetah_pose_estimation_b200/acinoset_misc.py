@@ -116,7 +116,9 @@ def _read_dlc_file(path, hand_labeled=False):
         return np.load(path).astype(np.float64), 0
     import pandas as pd
     if ext == ".csv":
-        df = pd.read_csv(path, header=[0, 1, 2], index_col=0)
+        # the three header rows (scorer / bodyparts / coords) are skipped rather than parsed: with header=[0, 1, 2] pandas
+        # takes an all-NaN first data row (an unlabelled frame) for the index-name row and drops it
+        df = pd.read_csv(path, header=None, skiprows=3, index_col=0)
     else:
         df = pd.read_hdf(path)          # raises ImportError without PyTables -- no silent substitute
     if not len(df.index):

@@ -3,7 +3,8 @@
 the `ipopt` call are replaced by the CUDA path (engine.Solver).  `solver_path` is accepted and ignored.
 
 Mirrored beyond the multi-view reconstruction: the monocular data-driven priors (`monocular_constraints=True`,
-SURVEY.md section 8f.1), pairwise pseudo-measurements (`enable_ppm`), hand-labelled detections, shutter-delay
+SURVEY.md section 8f.1), pairwise pseudo-measurements (`enable_ppm`), hand-labelled detections (`hand_labeled_data`:
+label tables named by image file, weighted-spline initial guess, `fte_kinematic_gt` output), shutter-delay
 estimation (`shutter_delay_estimation=True`, section 8f.4: engine.Solver.solve_shutter) and
 `CheetahEstimator.estimate_grf` (section 8f.3, first stage of the kinetic mode).  Not mirrored (out of scope,
 SURVEY.md section 8): `determine_contacts`, `estimate_kinetics` (full 54-row dynamics).

@@ -384,13 +384,15 @@ class Solver:
 
         Outer loop = augmented-Lagrangian multiplier updates with penalty continuation; inner loop = LM with
         per-sequence damping (all sequences advance in lock step; converged ones are masked and skipped).
-        Keywords: max_iter=40, n_outer=4, damp0=1e-3, ftol=1e-6, mu_schedule, check_every=1, skip_converged=True."""
+        Keywords: max_iter=40, n_outer=4, damp0=1e-3, ftol=1e-6, mu_schedule, check_every=4, skip_converged=True.
+        The host looks at the convergence flags (one device synchronisation) every `check_every` iterations only; the
+        iterations queued after every sequence has stopped are no-ops on the device, so results do not depend on it."""
         for _ in self.solve_steps(q0, **kw):
             pass
         return self.result
 
     def solve_steps(self, q0, max_iter=40, n_outer=4, damp0=1e-3, ftol=1e-6, mu_schedule=MU_SCHEDULE,
-                    check_every=1, skip_converged=True):
+                    check_every=4, skip_converged=True):
         """Generator form of `solve`: yields after the launches of every LM iteration have been queued (before the
         host looks at the convergence flags), so that a driver can interleave several solvers on different streams
         (`solve_split`).  The result dict is left in `self.result`."""

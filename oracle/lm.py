@@ -3,7 +3,8 @@
 Stands in for the reference's solver seam  `default_solver(...).solve(robot.m)`  (acinoset_opt.py:611-617;
 shared/physical_education/utils.py:459-548), which hands the NLP to IPOPT + MA97 -- neither is installed on
 this box, so optimiser parity is UNPINNED against IPOPT; this file is the FP64 CPU statement of the algorithm
-the CUDA path implements, used to check it step by step, and scipy (tests) cross-checks its optimum.
+the CUDA path implements, used to check it step by step; its optimum is cross-checked against an independent
+scipy SLSQP solve of the constrained NLP (oracle/nlp.py, tests/test_nlp_witness.py).
 
 One LM step, per sequence:
   1. frame-local Gauss-Newton blocks H_k[54,54], g_k[54]            (cost.frame_normal_equations)

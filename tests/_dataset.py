@@ -137,3 +137,28 @@ def write_pairwise_files(root, data_path, g, sync_offset=None, pad_frames=5):
             rows.append({"pose": pose, "pws": pws})
         with open(os.path.join(d, f"cam{c + 1}{misc.PW_SUFFIX}"), "wb") as f:
             pickle.dump(rows, f)
+
+
+def write_hand_labels(root, data_path, g, missing=()):
+    """`dlc_hand_labeled/cam<i>.csv` next to a clip built by `build_clip_dir`: DeepLabCut's CollectedData layout (3 header
+    rows, rows named by image file `img<frame>.png`, (x, y) per part, NaN = not labelled), one row per frame from 0 to the
+    end of the clip (the reference addresses these tables by row position = frame, acinoset_misc.py:216-221)."""
+    import pandas as pd
+    N, C = g["detections"].shape[:2]
+    start = int(g["start_frame"])
+    d = os.path.join(root, data_path, "dlc_hand_labeled")
+    os.makedirs(d, exist_ok=True)
+    parts = [f"part{i}" for i in range(25)]
+    for m, i in zip(sk.MARKERS, sk.DLC_INDEX):
+        parts[i] = m
+    cols = pd.MultiIndex.from_product([["labeller"], parts, ["x", "y"]], names=["scorer", "bodyparts", "coords"])
+    for c in range(C):
+        arr = np.full((start + N, 50), np.nan)
+        for l, i in enumerate(sk.DLC_INDEX):
+            arr[start:, 2 * i] = g["detections"][:, c, l, 0]
+            arr[start:, 2 * i + 1] = g["detections"][:, c, l, 1]
+        for (n, cc, l) in missing:
+            if cc == c:
+                arr[start + n, 2 * sk.DLC_INDEX[l]:2 * sk.DLC_INDEX[l] + 2] = np.nan
+        idx = [f"labeled-data/cam{c + 1}/img{f:03d}.png" for f in range(start + N)]
+        pd.DataFrame(arr, columns=cols, index=idx).to_csv(os.path.join(d, f"cam{c + 1}.csv"))

@@ -123,3 +123,27 @@ def test_shutter_delay_estimation_through_the_mirrored_api(golden_dir, tmp_path)
         got = df.to_numpy().reshape(len(df), 24, 3)[:, :, 0:2]                    # x, y, likelihood (NaN) per bodypart
         m = np.isfinite(got)
         assert m.mean() > 0.5 and np.abs(got[m] - uv[m]).max() < 1e-3
+
+
+def test_hand_labelled_reconstruction_through_the_mirrored_api(golden_dir, tmp_path):
+    """`init_trajectory(hand_labeled_data=True)` + `estimate_kinematics` (acinoset_opt.py:413-430, 539-635;
+    acinoset_misc.py:216-221, 425-439): (x, y) label tables named by image file, likelihood 1, NaN labels gated, the
+    weighted-spline initial guess, output into `fte_kinematic_gt`.  With labels equal to the clip's detections the result
+    is the plain reconstruction of that clip."""
+    from tests._dataset import write_hand_labels
+    from cheetah_pose_estimation_b200 import acinoset_misc as misc, acinoset_opt as opt
+    path = "2017_08_29/top/jules/run1_1"
+    g = np.load(os.path.join(golden_dir, "clip_jules_run1_1.npz"))
+    root = str(tmp_path)
+    build_clip_dir(root, path, g)
+    write_hand_labels(root, path, g, missing=[(3, 1, 7), (4, 1, 7), (10, 0, 2)])
+    est = opt.init_trajectory(root, path, "jules", kinetic_dataset=False, kinematic_model=True, hand_labeled_data=True)
+    assert est.meas.shape == g["detections"].shape[:2] + (24, 1, 4)
+    assert est.meas[3, 1, 7, 0, 2] == 0.0 and est.meas[3, 1, 8, 0, 2] == 1.0 and est.base_data.first_frame == [0] * 6
+    assert opt.estimate_kinematics(est, solver_output=False)
+    out = os.path.join(root, path, "fte_kinematic_gt", "fte.pickle")
+    assert os.path.exists(out)
+    d = pickle.load(open(out, "rb"))
+    mpjpe = misc.traj_error(d["positions"].copy(), g["positions"].copy(), centered=True).mean()
+    print(f"hand-labelled run: obj {d['obj_cost']:.3f}, MPJPE vs the shipped trajectory {mpjpe:.1f} mm")
+    assert mpjpe < 35.0
