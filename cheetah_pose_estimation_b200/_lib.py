@@ -94,6 +94,11 @@ EXPORTS = {
     "cpe_shutter_terms_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p, c_f64p, C.c_void_p]),
     "cpe_update_multipliers_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p,
                                              c_f64p, C.c_void_p]),
+    "cpe_motion_smoothing_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p, c_f64p, c_f64p,
+                                           C.c_void_p]),
+    "cpe_eom_slack_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p, c_f64p, c_f64p, C.c_void_p]),
+    "cpe_torque_costs_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, C.c_int32, c_f64p, c_f64p, c_f64p, c_f64p, c_f64p,
+                                       C.c_void_p]),
     "cpe_finalize_status_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, c_i32p, c_i32p, c_i32p, C.c_void_p]),
     "cpe_eval_host_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpeBatch), C.c_void_p, C.c_void_p, c_f64p,
                                     C.c_void_p, C.POINTER(CpeEvalOut), c_f64p, C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -112,3 +112,83 @@ def estimate_grf_states(fte_states, metadata, animal, iters=600, device="cuda"):
     grfz_est = {name: [float(v) for v in F[:, f]] for f, name in enumerate(FEET)}
     grfxy_est = {name: [[float(v) for v in row] for row in F[:, 4 + 4 * f:8 + 4 * f]] for f, name in enumerate(FEET)}
     return grfz_est, grfxy_est
+
+
+# ---- trajectory-level cost terms of the kinetic objective (acinoset_opt.py:905-921), cost + gradient on the GPU ------------
+def _dev_batch(S, N, h, n_frames, dev, chain_vec=None):
+    nf = torch.full((S,), N, dtype=torch.int32, device=dev) if n_frames is None else \
+        torch.as_tensor(n_frames, dtype=torch.int32, device=dev)
+    ht = torch.as_tensor(np.broadcast_to(np.asarray(h, np.float64), (S,)).copy(), device=dev)
+    b = _lib.CpeBatch()
+    b.S, b.N, b.C, b.W = S, N, 0, 1
+    b.n_frames, b.h = nf.data_ptr(), ht.data_ptr()
+    if chain_vec is not None:
+        b.chain_vec = chain_vec.data_ptr()
+    return b, (nf, ht)
+
+
+def _t(x, dev):
+    return torch.as_tensor(np.ascontiguousarray(x) if isinstance(x, np.ndarray) else x, dtype=torch.float64,
+                           device=dev).contiguous()
+
+
+def motion_smoothing(solver, q):
+    """misc.motion_smoothing_cost (acinoset_misc.py:601-613) of q[S,N,54] on the batch of `solver` (an engine.Solver):
+    returns (cost[S], grad[S,N,54]) as device tensors; fps = 1 / batch.h."""
+    lib, b = solver.lib, solver.b
+    pose = solver.evaluate(q, pose=True)["pose"]
+    S, N = q.shape[:2]
+    work = torch.zeros(S, N, dtype=torch.float64, device=q.device)
+    cost = torch.zeros(S, dtype=torch.float64, device=q.device)
+    grad = torch.zeros(S, N, 54, dtype=torch.float64, device=q.device)
+    bs = b.struct()
+    p = lambda x: C.c_void_p(x.data_ptr())
+    _lib.check(lib.cpe_motion_smoothing_f64(C.byref(solver.m.struct), C.byref(bs), p(q), p(pose), p(work), p(cost), p(grad),
+                                            C.c_void_p(torch.cuda.current_stream().cuda_stream)),
+               "cpe_motion_smoothing_f64")
+    return cost, grad
+
+
+def eom_slack(eom, Bm=None, n_frames=None, device="cuda"):
+    """misc.eom_slack_cost (acinoset_misc.py:631-636) on eom[S,N,6] (rows 0-5, `eom_rows`); with Bm[S,N,6,20] also the
+    gradient with respect to the forces.  Returns (cost[S], grad_F[S,N,20] or None)."""
+    lib = _lib.load()
+    dev = torch.device(device)
+    e = _t(eom, dev)
+    S, N = e.shape[:2]
+    B = None if Bm is None else _t(Bm, dev)
+    b, keep = _dev_batch(S, N, 1.0, n_frames, dev)
+    work = torch.zeros(S, N, dtype=torch.float64, device=dev)
+    cost = torch.zeros(S, dtype=torch.float64, device=dev)
+    g = None if B is None else torch.zeros(S, N, N_FORCES, dtype=torch.float64, device=dev)
+    p = lambda x: None if x is None else C.c_void_p(x.data_ptr())
+    _lib.check(lib.cpe_eom_slack_f64(C.byref(b), p(e), p(B), p(work), p(cost), p(g),
+                                     C.c_void_p(torch.cuda.current_stream().cuda_stream)), "cpe_eom_slack_f64")
+    return cost, g
+
+
+def torque_costs(Tc, weight, h, n_frames=None, device="cuda"):
+    """Torque terms on Tc[S,N,M] (all motors' axes flattened), weight[M], hm0 = h[S]: returns (cost[S,2], grad_sq, grad_ch)
+    with cost[:,0] = pe.motor.torque_squared_penalty (motor.py:412-417, 496-503) and cost[:,1] =
+    misc.change_in_torque_squared_cost (acinoset_misc.py:616-628)."""
+    lib = _lib.load()
+    dev = torch.device(device)
+    T = _t(Tc, dev)
+    S, N, M = T.shape
+    w = _t(np.broadcast_to(np.asarray(weight, np.float64), (M,)).copy(), dev)
+    b, keep = _dev_batch(S, N, h, n_frames, dev)
+    work = torch.zeros(2, S, N, dtype=torch.float64, device=dev)
+    cost = torch.zeros(S, 2, dtype=torch.float64, device=dev)
+    g1, g2 = torch.zeros_like(T), torch.zeros_like(T)
+    p = lambda x: C.c_void_p(x.data_ptr())
+    _lib.check(lib.cpe_torque_costs_f64(C.byref(b), p(T), C.c_int32(M), p(w), p(work), p(cost), p(g1), p(g2),
+                                        C.c_void_p(torch.cuda.current_stream().cuda_stream)), "cpe_torque_costs_f64")
+    return cost, g1, g2
+
+
+def kinetic_objective(kinematic_cost, pose_cost, torque_cost, smoothing_cost, slack_cost, fps, enable_eom_slack=True,
+                      disable_motion_prior=False):
+    """The reference's kinetic objective from its terms (acinoset_opt.py:905-921, use_2d_reprojections branch):
+    1e-3 (kinematic + pose + (torque + 0.1 fps^-2 smoothing) + 10e3 slack)."""
+    motion_prior = 0.0 if disable_motion_prior else torque_cost + 0.1 * fps ** -2 * smoothing_cost
+    return 1e-3 * (kinematic_cost + pose_cost + motion_prior + 10e3 * (slack_cost if enable_eom_slack else 0.0))

@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 114          /* 0.1.14 */
+#define CPE_VERSION 115          /* 0.1.15 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -329,6 +329,22 @@ int cpe_eom_affine_f64(const cpe_batch *batch, const double *q, const double *dq
  * optimum value to ~1e-14 ||a|| on the fixture).  grf[S,N,20], resid[S,N] = the optimal || eom ||. */
 int cpe_grf_solve_f64(const cpe_batch *batch, const double *a, const double *Bm, const int32_t *contact, int32_t iters,
                       double *grf, double *resid, void *stream);
+
+/* Trajectory-level cost terms of the kinetic objective (acinoset_opt.py:905-921), each with its gradient.  Frame ranges
+ * follow the reference's code (1-based `fe < nfe - 2` / `fe < nfe - 1`: one term fewer than the data allows).
+ * cpe_motion_smoothing_f64: misc.motion_smoothing_cost (acinoset_misc.py:601-613) with fps = 1 / batch->h[s]; pose[S,N,24,3]
+ *   = cpe_eval_out.pose of the same q; cost[S]; grad[S,N,54] = d cost / d q (may be NULL); frame_work[S,N] scratch.
+ * cpe_eom_slack_f64: misc.eom_slack_cost (:631-636) on eom[S,N,6] of cpe_eom_f64; with Bm[S,N,6,20] of cpe_eom_affine_f64
+ *   also grad_f[S,N,20] = d cost / d F = -2 Bm^T eom (both may be NULL).
+ * cpe_torque_costs_f64: Tc[S,N,n_axes] joint torques; cost[S,2] = { sum (weight Tc)^2 (motor.py:412-417, 496-503),
+ *   sum ((Tc[fe+1] - Tc[fe]) / hm0)^2 with hm0 = batch->h[s] (acinoset_misc.py:616-628) }; grad_sq, grad_ch [S,N,n_axes]
+ *   (may be NULL); frame_work[2,S,N] scratch. */
+int cpe_motion_smoothing_f64(const cpe_model *model, const cpe_batch *batch, const double *q, const double *pose,
+                             double *frame_work, double *cost, double *grad, void *stream);
+int cpe_eom_slack_f64(const cpe_batch *batch, const double *eom, const double *Bm, double *frame_work, double *cost,
+                      double *grad_f, void *stream);
+int cpe_torque_costs_f64(const cpe_batch *batch, const double *Tc, int32_t n_axes, const double *weight, double *frame_work,
+                         double *cost, double *grad_sq, double *grad_ch, void *stream);
 
 /* Shutter-delay estimation (acinoset_misc.py:182-183, 273-286): the pieces that are not per-residual work.
  * cpe_base_rates_f64: dq_base, ddq_base [S,N,3] of q in the q-only formulation -- backward differences of the base
