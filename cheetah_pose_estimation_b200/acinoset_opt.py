@@ -6,8 +6,8 @@ Mirrored beyond the multi-view reconstruction: the monocular data-driven priors 
 SURVEY.md section 8f.1), pairwise pseudo-measurements (`enable_ppm`), hand-labelled detections (`hand_labeled_data`:
 label tables named by image file, weighted-spline initial guess, `fte_kinematic_gt` output), shutter-delay
 estimation (`shutter_delay_estimation=True`, section 8f.4: engine.Solver.solve_shutter) and
-`CheetahEstimator.estimate_grf` (section 8f.3, first stage of the kinetic mode).  Not mirrored (out of scope,
-SURVEY.md section 8): `determine_contacts`, `estimate_kinetics` (full 54-row dynamics).
+`CheetahEstimator.estimate_grf` and `determine_contacts` (section 8f.3, first stages of the kinetic mode).  Not mirrored
+(out of scope): `estimate_kinetics` (full 54-row dynamics).
 """
 import json
 import os
@@ -227,8 +227,35 @@ def init_trajectory(root_dir: str,
         est.base_data = misc.load_dlc_arrays(dlc_dir, scene.n_cams, hand_labeled=hand_labeled_data)
         pw_data = misc.load_pairwise(dlc_dir, scene.n_cams) if enable_ppm else None
         est.meas, est.cams_used = misc.pack_measurements(params, scene, est.base_data, pw_data)
-    _ = (ground_plane_height, disable_contact_lcp, bound_eom_error, solver_path)     # kinetic-mode / IPOPT settings
+    est.ground_plane_height = float(ground_plane_height)      # Foot3D.ground_plane_height (acinoset_opt.py:500)
+    _ = (disable_contact_lcp, bound_eom_error, solver_path)                           # kinetic-mode / IPOPT settings
     return est
+
+
+def determine_contacts(estimator: CheetahEstimator, monocular: bool = False, verbose: bool = True,
+                       out_dir_prefix: Optional[str] = None):
+    """Reference: determine_contacts (acinoset_opt.py:638-690).  Reads the kinematic trajectory saved by
+    `estimate_kinematics` (`fte_kinematic[_<cam>]/fte.pickle`), runs the contact heuristic on the CPU as the reference does
+    (kinetics.contact_detection = misc.contact_detection, acinoset_misc.py:745-856) and writes `grf/autogen-contact.json`
+    and `grf/autogen-contact-02.json`, the files `estimate_grf` reads.  The synthetic GRF tables of `misc.synth_grf_data`
+    (initial guesses of the kinetic NLP) are not produced: that NLP is out of scope here.  Returns (contacts, contacts_tmp)."""
+    import pickle
+    from . import kinetics
+    data_dir = estimator.params.data_dir if out_dir_prefix is None else os.path.join(
+        out_dir_prefix, estimator.params.data_dir.split("cheetah_videos")[1][1:])
+    sub = "fte_kinematic" if not monocular else f"fte_kinematic_{estimator.scene.cam_idx}"
+    with open(os.path.join(data_dir, sub, "fte.pickle"), "rb") as f:
+        fte_states = pickle.load(f)
+    estimator.com_vel, estimator.com_pos = fte_states["com_vel"], fte_states["com_pos"]
+    contacts, contacts_tmp = kinetics.determine_contacts_from_states(
+        fte_states, estimator.name, estimator.params.start_frame, estimator.scene.fps,
+        getattr(estimator, "ground_plane_height", 0.0), data_dir)
+    if verbose:
+        print("Height, velocity, stance time heuristic:")
+        print(contacts)
+        print("Height:")
+        print(contacts_tmp)
+    return contacts, contacts_tmp
 
 
 def initial_guess(estimator: CheetahEstimator) -> np.ndarray:

@@ -192,3 +192,124 @@ def kinetic_objective(kinematic_cost, pose_cost, torque_cost, smoothing_cost, sl
     1e-3 (kinematic + pose + (torque + 0.1 fps^-2 smoothing) + 10e3 slack)."""
     motion_prior = 0.0 if disable_motion_prior else torque_cost + 0.1 * fps ** -2 * smoothing_cost
     return 1e-3 * (kinematic_cost + pose_cost + motion_prior + 10e3 * (slack_cost if enable_eom_slack else 0.0))
+
+
+# ---- contact detection (CPU, as in the reference: acinoset_opt.py:638-690 -> acinoset_misc.py:745-856) --------------------
+PAW_MARKERS = {"HFL_foot": "l_front_paw", "HFR_foot": "r_front_paw", "HBL_foot": "l_back_paw", "HBR_foot": "r_back_paw"}
+
+
+def foot_height_and_velocity(q, dq, lengths, radii):
+    """Foot positions and velocities of the four feet, [N,4,3] each, in FEET order: the foot point of the reference's
+    `Foot3D` is the bottom of the H link = the paw marker (cheetah.py:96-101, acinoset_misc.py:1640-1659), and its velocity
+    `Pb_I_vel = J dq` (foot.py:394-395) is the time derivative of that position along the saved dq."""
+    q, dq = np.asarray(q, np.float64), np.asarray(dq, np.float64)
+    chain_link, chain_vec = skeleton.marker_chains(lengths, radii)
+    idx = [skeleton.MARKERS.index(PAW_MARKERS[f]) for f in FEET]
+    ang, dang = q[:, 3:].reshape(-1, 17, 3), dq[:, 3:].reshape(-1, 17, 3)
+    sf, cf, st, ct, sp, cp = (np.sin(ang[..., 0]), np.cos(ang[..., 0]), np.sin(ang[..., 1]), np.cos(ang[..., 1]),
+                              np.sin(ang[..., 2]), np.cos(ang[..., 2]))
+    z = np.zeros_like(sf)
+    R = np.stack([np.stack([cp * ct, cp * st * sf - sp * cf, cp * st * cf + sp * sf], -1),
+                  np.stack([sp * ct, sp * st * sf + cp * cf, sp * st * cf - cp * sf], -1),
+                  np.stack([-st, ct * sf, ct * cf], -1)], -2)                               # [N,17,3,3]
+    dRf = np.stack([np.stack([z, cp * st * cf + sp * sf, -cp * st * sf + sp * cf], -1),
+                    np.stack([z, sp * st * cf - cp * sf, -sp * st * sf - cp * cf], -1),
+                    np.stack([z, ct * cf, -ct * sf], -1)], -2)
+    dRt = np.stack([np.stack([-cp * st, cp * ct * sf, cp * ct * cf], -1),
+                    np.stack([-sp * st, sp * ct * sf, sp * ct * cf], -1),
+                    np.stack([-ct, -st * sf, -st * cf], -1)], -2)
+    dRp = np.stack([np.stack([-sp * ct, -sp * st * sf - cp * cf, -sp * st * cf + cp * sf], -1),
+                    np.stack([cp * ct, cp * st * sf - sp * cf, cp * st * cf + sp * sf], -1),
+                    np.stack([z, z, z], -1)], -2)
+    Rdot = dRf * dang[..., 0, None, None] + dRt * dang[..., 1, None, None] + dRp * dang[..., 2, None, None]
+    pos = np.zeros((q.shape[0], 4, 3))
+    vel = np.zeros((q.shape[0], 4, 3))
+    for f, l in enumerate(idx):
+        pos[:, f], vel[:, f] = q[:, 0:3], dq[:, 0:3]
+        for j in range(skeleton.MAX_CHAIN):
+            link = int(chain_link[l, j])
+            if link >= 0:
+                pos[:, f] += R[:, link] @ chain_vec[l, j]
+                vel[:, f] += Rdot[:, link] @ chain_vec[l, j]
+    return pos, vel
+
+
+def _positive_zero_crossings(x):
+    """acinoset_misc.py:2033-2046 (indices refer to the array with exact zeros removed, as in the reference)."""
+    x = x[np.nonzero(x)]
+    out = []
+    for i in range(1, len(x)):
+        if x[i - 1] < 0 and x[i] > 0:
+            out += [i + 2, i + 1, i, i - 1, i - 2]
+    return out
+
+
+def _group_by_consecutive_values(x):
+    spl = [0] + [i for i in range(1, len(x)) if x[i] - x[i - 1] > 1] + [None]
+    return [x[b:e] for (b, e) in [(spl[i - 1], spl[i]) for i in range(1, len(spl))]]
+
+
+def contact_detection(foot_height, foot_vel_z, start_frame, speed, fps, ground_plane_height=0.0, data_dir=None):
+    """misc.contact_detection (acinoset_misc.py:745-856) on foot_height[N,4] and the vertical foot velocity [N,4] (FEET
+    order): stance length from the speed (linear model through (9 m/s, 0.09 s), (14 m/s, 0.06 s)), a 5 cm height
+    threshold above the ground plane, and a positive zero crossing of the vertical velocity near the height minimum.
+    Returns (contacts, contacts_tmp) and, with `data_dir`, writes `grf/autogen-contact.json` / `autogen-contact-02.json`."""
+    import json
+    import os
+    n = foot_height.shape[0]
+    m_, c_ = np.linalg.lstsq(np.vstack([[9.0, 14.0], [1.0, 1.0]]).T, [0.09, 0.06], rcond=None)[0]
+    stance_time_fe = round((m_ * speed + c_) * fps)
+    mid_way = stance_time_fe // 2
+    is_even = (stance_time_fe % 2) == 0
+    contacts, contacts_tmp = {}, {}
+    for i, name in enumerate(FEET):
+        h = foot_height[:, i]
+        under = _group_by_consecutive_values(np.where(h < ground_plane_height + 0.05)[0])
+        crossings = _positive_zero_crossings(foot_vel_z[:, i])
+        contacts[name], contacts_tmp[name] = [], []
+        arg_min = -1
+        for j, grp in enumerate(under):
+            if len(grp) == 0:
+                continue
+            lo = int(arg_min + 1)
+            hi = under[j + 1][0] if j + 1 < len(under) else -1
+            arg_min = lo + int(np.argmin(h[lo:hi]))
+            possible = np.intersect1d(grp, crossings)
+            if all(arg_min + k not in possible for k in (-2, -1, 0, 1, 2)):
+                arg_min = grp[-1]
+                continue
+            start_idx, end_idx = int(arg_min - mid_way), int(arg_min + mid_way)
+            arg_min = grp[-1]
+            if is_even:
+                start_idx += 1
+            if start_idx < 0:
+                end_idx -= start_idx
+                start_idx = 0
+            if end_idx >= n:
+                start_idx -= end_idx - n - 1
+                end_idx = n - 1
+            contacts[name].append([int(start_frame + start_idx), int(start_frame + end_idx), i, "TBD"])
+            contacts_tmp[name].append([int(start_frame + grp[0]), int(start_frame + grp[-1]), i, "TBD"])
+        if not contacts[name]:
+            contacts[name] = contacts_tmp[name] = None
+    for a, b in (("HFL_foot", "HFR_foot"), ("HBL_foot", "HBR_foot")):          # rotary gallop: first contact = trailing limb
+        if contacts[a] is not None and contacts[b] is not None:
+            first_a = contacts[a][0][0] > contacts[b][0][0]
+            contacts[a][0][3] = "leading" if first_a else "trailing"
+            contacts[b][0][3] = "trailing" if first_a else "leading"
+    if data_dir is not None:
+        grf_dir = os.path.join(data_dir, "grf")
+        os.makedirs(grf_dir, exist_ok=True)
+        for fname, c in (("autogen-contact.json", contacts), ("autogen-contact-02.json", contacts_tmp)):
+            with open(os.path.join(grf_dir, fname), "w", encoding="utf-8") as f:
+                json.dump({"start_frame": int(start_frame), "end_frame": int(start_frame + n), "contacts": c}, f)
+    return contacts, contacts_tmp
+
+
+def determine_contacts_from_states(fte_states, animal, start_frame, fps, ground_plane_height=0.0, data_dir=None):
+    """opt.determine_contacts (acinoset_opt.py:638-690) from the dict of a saved fte.pickle: foot heights / velocities from
+    q, dq, speed = mean norm of `com_vel`."""
+    lengths, radii, _ = skeleton.animal(animal)
+    pos, vel = foot_height_and_velocity(fte_states["q"], fte_states["dq"], lengths, radii)
+    speed = float(np.mean(np.linalg.norm(np.asarray(fte_states["com_vel"]), axis=1)))
+    return contact_detection(pos[:, :, 2], vel[:, :, 2], start_frame, speed, fps, ground_plane_height, data_dir)

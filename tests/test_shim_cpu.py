@@ -265,3 +265,41 @@ def test_base_rates_match_the_oracle_and_the_collocation_rows():
     assert np.abs(b[1:] - b[:-1] - h[0] * vv[1:]).max() < 1e-14          # q_n = q_{n-1} + h dq_n
     assert np.abs(vv[1:] - vv[:-1] - h[0] * aa[1:]).max() < 1e-10        # dq_n = dq_{n-1} + h ddq_n, incl. the first node
     assert np.array_equal(aa[0], aa[1]) and np.array_equal(aa[1], aa[2])
+
+
+def test_contact_detection_reproduces_the_shipped_contact_files(golden_dir):
+    """kinetics.contact_detection (= misc.contact_detection, acinoset_misc.py:745-856, driven as opt.determine_contacts
+    does, acinoset_opt.py:638-690) on the shipped monocular trajectories of all ten clips: both shipped contact files
+    (`autogen-contact.json`: height + velocity + stance-time heuristic with leading / trailing labels;
+    `autogen-contact-02.json`: height threshold only) come back exactly.  The clip's ground-plane height is the one input
+    the shipped files do not carry; the fixture holds the value the second file pins (oracle/make_golden_contacts.py)."""
+    import json
+    from cheetah_pose_estimation_b200 import kinetics
+    g = np.load(os.path.join(golden_dir, "contacts_ref.npz"))
+    assert len(g["names"]) == 10
+    for i, name in enumerate(g["names"]):
+        st = {"q": g[f"{i}_q"], "dq": g[f"{i}_dq"], "com_vel": g[f"{i}_com_vel"]}
+        c, c2 = kinetics.determine_contacts_from_states(st, str(g[f"{i}_animal"]), int(g[f"{i}_start_frame"]),
+                                                        float(g[f"{i}_fps"]), float(g[f"{i}_ground"]))
+        assert c == json.loads(str(g[f"{i}_contacts"])), name
+        assert c2 == json.loads(str(g[f"{i}_contacts_02"])), name
+        lo, hi = g[f"{i}_ground_interval"]
+        assert 0.002 < hi - lo < 0.02                      # the height-only file pins the ground plane to millimetres
+
+
+def test_foot_velocity_is_the_time_derivative_of_the_foot_position(golden_dir):
+    from cheetah_pose_estimation_b200 import kinetics
+    g = np.load(os.path.join(golden_dir, "contacts_ref.npz"))
+    lengths, radii, _ = sk.animal("jules")
+    q, dq = g["0_q"][:5], g["0_dq"][:5]
+    pos, vel = kinetics.foot_height_and_velocity(q, dq, lengths, radii)
+    eps = 1e-6
+    pp, _ = kinetics.foot_height_and_velocity(q + eps * dq, dq, lengths, radii)
+    pm, _ = kinetics.foot_height_and_velocity(q - eps * dq, dq, lengths, radii)
+    assert np.abs((pp - pm) / (2 * eps) - vel).max() < 1e-6 * max(1.0, np.abs(vel).max())
+    # the foot point is the paw marker of the pose function (acinoset_misc.py:1640-1659)
+    from oracle import kinematics
+    cl, cv = kinematics.marker_chains(lengths, radii)
+    pose = kinematics.fk(q, cl, cv)
+    for f, name in enumerate(kinetics.FEET):
+        assert np.abs(pose[:, sk.MARKERS.index(kinetics.PAW_MARKERS[name])] - pos[:, f]).max() < 1e-13
