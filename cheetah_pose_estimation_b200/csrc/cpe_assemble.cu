@@ -401,7 +401,8 @@ __global__ void __launch_bounds__(TEAM_T *NTEAM, 1) assemble_kernel(const __grid
     team_sync<TEAM_T>(team);
     // ---- reduced block S = H_ii + damping - sum_g Hdi^T Y and ghat = g_i - sum_g Hdi^T y (static gather) ----------------
     double *So = p.ao.S + fidx * 784;
-    for (int eo = tid; eo < 28 * 29; eo += nt) {
+    const int n_swork = p.m.k2_off[42];               // lower triangle of S + the reduced gradient
+    for (int eo = tid; eo < n_swork; eo += nt) {
         const uint32_t m = t_smeta[eo];
         const int r = m & 31, c = (m >> 5) & 31, ns = (m >> 10) & 7, si = m >> 13;
         double v = si != 1023 ? ENT[si] : 0.0;
@@ -416,8 +417,12 @@ __global__ void __launch_bounds__(TEAM_T *NTEAM, 1) assemble_kernel(const __grid
             for (int ii = 0; ii < GD; ++ii) sacc += D[ii * GN] * Yc[ii * (GN + 1)];
             v -= sacc;
         }
-        if (c == 28) p.ao.ghat[fidx * 28 + r] = v;
-        else So[r * 28 + c] = v;
+        if (c == 28) {
+            p.ao.ghat[fidx * 28 + r] = v;
+        } else {
+            So[r * 28 + c] = v;
+            if (r != c) So[c * 28 + r] = v;               // S is symmetric: one evaluation, two stores
+        }
     }
     team_sync<TEAM_T>(team);       // the next frame overwrites this team's scratch
     }   // frames of this team

@@ -518,13 +518,16 @@ def k2_tables(a, ind_idx):
     la = lists(a["ent_order"], a["a_ptr"], a["a_items"])
     le = lists(a["ent_order"], a["e_ptr"], a["e_items"])
     li = lists(a["ent_order"], a["i_ptr"], a["i_items"])
-    ls_ = lists(a["s_order"], a["s_ptr"], a["s_items"])
+    # Schur work items: S is symmetric, so only its lower triangle (c <= r) and the reduced gradient (c = 28) are
+    # computed; the kernel mirrors each value on store (which also makes S bitwise symmetric)
+    s_work = [int(e) for e in a["s_order"] if (int(e) % (N_IND + 1)) <= (int(e) // (N_IND + 1)) or int(e) % (N_IND + 1) == N_IND]
+    ls_ = lists(s_work, a["s_ptr"], a["s_items"])
     meta = np.zeros((K2_ENT_PAD, 2), np.uint32)
     for eo, e in enumerate(a["ent_order"]):
         pq = int(a["ent_pq"][int(e)])
         meta[eo] = (int(e) | ((pq >> 6) << 10) | ((pq & 63) << 16), len(la[eo]) | (len(le[eo]) << 8) | (len(li[eo]) << 16))
     smeta = np.zeros(K2_S_PAD, np.uint32)
-    for eo, e in enumerate(a["s_order"]):
+    for eo, e in enumerate(s_work):
         r, c = divmod(int(e), N_IND + 1)
         src = int(a["grad_ent"][int(ind_idx[r])]) if c == N_IND else int(a["s_src"][r * N_IND + c])
         smeta[eo] = r | (c << 5) | (len(ls_[eo]) << 10) | ((src if src >= 0 else 1023) << 13)
@@ -546,4 +549,5 @@ def k2_tables(a, ind_idx):
     off.append(pos)
     k2_off = np.zeros(48, np.int32)
     k2_off[:len(off)] = off
-    return dict(k2_tab=np.concatenate(blob), k2_off=k2_off)
+    k2_off[K2_OFF_END + 1] = len(s_work)                      # number of Schur work items (434)
+    return dict(k2_tab=np.concatenate(blob), k2_off=k2_off, k2_s_work=np.array(s_work, np.int32))

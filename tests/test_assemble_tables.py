@@ -152,8 +152,10 @@ def test_k2_table_blob_holds_the_same_lists_in_processing_order():
                 assert eo < len(slots[i]) and int(slots[i][eo]) == int(lst[i])
     sm = sec(sk.K2_OFF_SMETA, np.uint32)
     s_slots = [sec(sk.K2_OFF_S + i, np.uint16) for i in range(sk.K2_MAX_S)]
-    for eo, e in enumerate(at["s_order"]):
-        e = int(e)
+    work = [int(e) for e in at["k2_s_work"]]
+    assert int(off[sk.K2_OFF_END + 1]) == len(work) == 28 * 29 // 2 + 28             # lower triangle of S + ghat
+    assert work == [int(e) for e in at["s_order"] if int(e) % 29 <= int(e) // 29 or int(e) % 29 == 28]
+    for eo, e in enumerate(work):
         r, c = divmod(e, 29)
         m = int(sm[eo])
         assert (m & 31, (m >> 5) & 31) == (r, c)

@@ -177,3 +177,37 @@ def test_run_dataset_cli_on_two_gpus_matches_one(golden_dir, tmp_path):
                 d1, d2 = pickle.load(open(p1, "rb")), pickle.load(open(p2, "rb"))
                 assert np.array_equal(d1["q"], d2["q"]) and d1["obj_cost"] == d2["obj_cost"], (c["name"], sub)
     assert os.path.exists(os.path.join(outs[2], "dataset_results.csv"))
+
+
+def test_run_monocular_all_and_ablation_on_a_subset(golden_dir, tmp_path):
+    """`run_monocular_all` (run_dataset.py:918-1015: every clip x every camera of its camera space x two test types) and
+    `run_data_driven_ablation_study` (:635-717) on two clips: one ragged batch of camera hypotheses per test type, output
+    directories per camera, the ablation's four prior scenarios with errors against the multi-view reconstruction."""
+    from cheetah_pose_estimation_b200 import run_dataset
+    clips = [c for c in load_test_set_clips(golden_dir) if c["name"] in
+             ("2017_08_29/top/jules/run1_1", "2019_03_03/phantom/run")]
+    root = _build_root(tmp_path, clips)
+    subset = tuple(t for t in run_dataset.DATASET if run_dataset._data_path(t) in [c["name"] for c in clips])
+    assert len(subset) == 2
+    out = os.path.join(str(tmp_path), "out")
+    models_dir = os.path.join(str(tmp_path), "models", "data-driven")
+    write_data_driven_dataset(golden_dir, models_dir)
+    cam_space = {"2019_03_03/phantom/run": (0, 1, 2, 3), "2017_08_29/top/jules/run1_1": (0, 2, 5)}
+    spaces = tuple(cam_space[run_dataset._data_path(t)] for t in subset)
+    oks = run_dataset.run_monocular_all(root, out, subset, models_dir=models_dir, cam_space=spaces)
+    assert len(oks["default"]) == 7 and len(oks["data-driven"]) == 7
+    i = 0
+    for t, space in zip(subset, spaces):
+        for cam in space:
+            if oks["default"][i]:
+                assert os.path.exists(os.path.join(out, run_dataset._data_path(t), f"fte_kinematic_orig_{cam}", "fte.pickle"))
+            if oks["data-driven"][i]:
+                d = pickle.load(open(os.path.join(out, run_dataset._data_path(t), f"fte_kinematic_{cam}", "fte.pickle"), "rb"))
+                assert d["meas_err"].shape[1] == 1
+            i += 1
+    assert sum(oks["data-driven"]) >= 5, oks
+    # the ablation study needs the multi-view reconstruction as its reference
+    run_dataset.run_monocular(root, out, subset, None, models_dir=models_dir, test_types=("ground-truth",))
+    res = run_dataset.run_data_driven_ablation_study(root, out, subset, models_dir=models_dir)
+    assert len(res["mpjpe"]) == 4 and all(np.isfinite(res["mpjpe"])) and os.path.exists(os.path.join(out, "data_driven_ablation.pickle"))
+    print("ablation (pose off+motion off, pose off, motion off, both on): MPJPE", np.round(res["mpjpe"], 1), "MPE", np.round(res["mpe"], 1))
