@@ -97,6 +97,7 @@ EXPORTS = {
     "cpe_motion_smoothing_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p, c_f64p, c_f64p,
                                            C.c_void_p]),
     "cpe_eom_slack_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p, c_f64p, c_f64p, C.c_void_p]),
+    "cpe_eom_slack_noalloc_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p, c_f64p, C.c_void_p]),
     "cpe_torque_costs_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, C.c_int32, c_f64p, c_f64p, c_f64p, c_f64p, c_f64p,
                                        C.c_void_p]),
     "cpe_finalize_status_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, c_i32p, c_i32p, c_i32p, C.c_void_p]),
@@ -130,5 +131,6 @@ def load():
 
 def check(rc, what):
     if rc != 0:
-        kind = "argument error" if rc < 0 else "CUDA error"
+        kind = ("problem exceeds the static scratch of a *_noalloc entry point" if rc == -4 else
+                "argument error" if rc < 0 else "CUDA error")
         raise CpeError(f"{what} failed: {kind} {rc}")

@@ -162,6 +162,54 @@ extern "C" int cpe_eom_slack_f64(const cpe_batch *b, const double *eom, const do
     return (int)cudaGetLastError();
 }
 
+// ---- allocation-free variant of cpe_eom_slack_f64 ---------------------------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops, harnesses that forbid it).  The per-frame scratch `frame_work` lives in a
+// file-scope device array of CPE_NOALLOC_MAX_FRAMES doubles (512 KB, held by every GPU that loads the library until exit).
+// In HOST code the array's name is a host-side stand-in, not a device address: the address is obtained once per device, with
+// that device current, through cudaGetSymbolAddress and cached; the kernels get that pointer.
+static __device__ __align__(256) double g_noalloc_frame_work[CPE_NOALLOC_MAX_FRAMES];
+
+namespace cpe {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static double *g_noalloc_ptr[NOALLOC_MAX_DEVICES];      // device address of the scratch, per device ordinal (0 = not set up)
+
+static int noalloc_scratch(double **out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return CPE_E_ARG;
+    double *p = __atomic_load_n(&g_noalloc_ptr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        // set-up, once per device, with that device current (two threads racing here obtain the same address)
+        e = cudaGetSymbolAddress((void **)&p, g_noalloc_frame_work);
+        if (e != cudaSuccess) return (int)e;
+        if (!p) return CPE_E_NULL;
+        __atomic_store_n(&g_noalloc_ptr[dev], p, __ATOMIC_RELEASE);
+    }
+    *out = p;
+    return 0;
+}
+}  // namespace cpe
+
+extern "C" int cpe_eom_slack_noalloc_f64(const cpe_batch *b, const double *eom, const double *Bm, double *cost,
+                                         double *grad_f, void *stream) {
+    if (!b || !eom || !cost || !b->n_frames) return CPE_E_NULL;
+    if (b->S <= 0 || b->N <= 0) return CPE_E_DIM;
+    const long long frames = (long long)b->S * b->N;
+    if (frames > CPE_NOALLOC_MAX_FRAMES) return CPE_E_SCRATCH;          // beyond the static scratch: use cpe_eom_slack_f64
+    double *work = nullptr;
+    const int rc = cpe::noalloc_scratch(&work);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    // the array keeps the previous call's contents: the part this call uses starts at zero
+    cudaError_t e = cudaMemsetAsync(work, 0, (size_t)frames * sizeof(double), st);
+    if (e != cudaSuccess) return (int)e;
+    cpe::eom_slack_kernel<<<(unsigned)((frames + 3) / 4), 128, 0, st>>>(b->S, b->N, b->n_frames, eom, Bm, work, grad_f);
+    cpe::reduce_frames_kernel<<<b->S, 128, 0, st>>>(b->S, b->N, b->n_frames, work, cost, 1, 0);
+    return (int)cudaGetLastError();
+}
+
 extern "C" int cpe_torque_costs_f64(const cpe_batch *b, const double *Tc, int32_t n_axes, const double *weight,
                                     double *frame_work, double *cost, double *grad_sq, double *grad_ch, void *stream) {
     if (!b || !Tc || !weight || !frame_work || !cost || !b->n_frames || !b->h) return CPE_E_NULL;

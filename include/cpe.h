@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 115          /* 0.1.15 */
+#define CPE_VERSION 116          /* 0.1.16 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -75,6 +75,7 @@ extern "C" {
 #define CPE_E_ARG (-1)
 #define CPE_E_DIM (-2)
 #define CPE_E_NULL (-3)
+#define CPE_E_SCRATCH (-4)       /* the problem exceeds the static scratch of a *_noalloc entry point */
 
 /* Static skeleton tables (device pointers; built once on the host from the chain topology). */
 typedef struct cpe_model {
@@ -345,6 +346,18 @@ int cpe_eom_slack_f64(const cpe_batch *batch, const double *eom, const double *B
                       double *grad_f, void *stream);
 int cpe_torque_costs_f64(const cpe_batch *batch, const double *Tc, int32_t n_axes, const double *weight, double *frame_work,
                          double *cost, double *grad_sq, double *grad_ch, void *stream);
+
+/* Allocation-free variant of cpe_eom_slack_f64.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same inputs and outputs as cpe_eom_slack_f64 minus `frame_work`: the per-frame scratch is a static device
+ * array inside the library, CPE_NOALLOC_MAX_FRAMES doubles (512 KB per GPU that loads the library, held until exit).
+ * Returns CPE_E_SCRATCH when S * N exceeds CPE_NOALLOC_MAX_FRAMES (use cpe_eom_slack_f64 with caller scratch then).
+ * Calls no cudaMalloc / cudaFree / allocating routine; results are bit-identical to cpe_eom_slack_f64.
+ * EVERY call on a device shares that one array (the part a call uses is cleared first, on `stream`): calls that overlap
+ * on the GPU -- different streams, or graphs replayed concurrently -- RACE; serialise them. */
+#define CPE_NOALLOC_MAX_FRAMES 65536
+int cpe_eom_slack_noalloc_f64(const cpe_batch *batch, const double *eom, const double *Bm, double *cost, double *grad_f,
+                              void *stream);
 
 /* Shutter-delay estimation (acinoset_misc.py:182-183, 273-286): the pieces that are not per-residual work.
  * cpe_base_rates_f64: dq_base, ddq_base [S,N,3] of q in the q-only formulation -- backward differences of the base
