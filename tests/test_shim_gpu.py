@@ -46,14 +46,19 @@ def test_kinematic_reconstruction_of_a_real_clip(golden_dir, tmp_path, animal, f
     sv = engine.Solver(est.model, batch, with_solver=False)
     c_ship = sv.evaluate(torch.as_tensor(g["q"][None].copy(), device="cuda"))["cost"][0].cpu().numpy()
     obj_ship = 1e-3 * (c_ship[0] + c_ship[1])
-    assert d["obj_cost"] <= obj_ship * 1.005, (d["obj_cost"], obj_ship)
+    # two-sided (measured, profiles/r2b_run_dataset.log: 38.209 / 39.358 and 83.397 / 84.801, i.e. 1.7-2.9 % below the
+    # shipped trajectory's cost under the same all-on objective): not worse, and not a different problem
+    assert 0.95 * obj_ship <= d["obj_cost"] <= obj_ship * 1.005, (d["obj_cost"], obj_ship)
+    assert np.abs(est.result["c_eq"]).max() < 5e-5            # feasibility at the level of the shipped IPOPT optima
     # (iii) distance to the shipped trajectory (different likelihood mask => not identical)
     mpjpe = misc.traj_error(d["positions"].copy(), g["positions"].copy(), centered=True).mean()
     mpe = misc.traj_error(d["positions"].copy(), g["positions"].copy()).mean()
     print(f"{path}: obj {d['obj_cost']:.3f} (shipped trajectory under the same objective {obj_ship:.3f}; shipped "
           f"obj_cost {float(g['obj_cost']):.3f} with the lost mask), MPJPE {mpjpe:.1f} mm, MPE {mpe:.1f} mm, "
           f"{d['processing_time_s']:.3f} s vs IPOPT {float(g['processing_time_s']):.1f} s")
-    assert mpjpe < 30.0 and mpe < 60.0
+    # measured 18.8 / 21.6 mm (jules run1_1) and 19.7 / 21.7 mm (phantom run) from the shipped trajectory, whose
+    # likelihood mask is lost (the 1 mm bar is checked against the NLP witness on identical inputs)
+    assert mpjpe < 25.0 and mpe < 28.0
 
 
 def test_monocular_reconstruction_with_data_driven_priors(golden_dir, tmp_path):
