@@ -384,7 +384,9 @@ class Solver:
 
         Outer loop = augmented-Lagrangian multiplier updates with penalty continuation; inner loop = LM with
         per-sequence damping (all sequences advance in lock step; converged ones are masked and skipped).
-        Keywords: max_iter=40, n_outer=4, damp0=1e-3, ftol=1e-6, mu_schedule, check_every=4, skip_converged=True.
+        Keywords: max_iter=40, n_outer=4, damp0=1e-3, ftol=1e-6, mu_schedule, check_every=4, skip_converged=True,
+        graph=False (True: one CUDA graph per multiplier round replays the iteration's launches -- for small batches,
+        where the loop is launch-bound; bit-identical results).
         The host looks at the convergence flags (one device synchronisation) every `check_every` iterations only; the
         iterations queued after every sequence has stopped are no-ops on the device, so results do not depend on it."""
         for _ in self.solve_steps(q0, **kw):
@@ -392,21 +394,30 @@ class Solver:
         return self.result
 
     def solve_steps(self, q0, max_iter=40, n_outer=4, damp0=1e-3, ftol=1e-6, mu_schedule=MU_SCHEDULE,
-                    check_every=4, skip_converged=True):
+                    check_every=4, skip_converged=True, graph=False):
         """Generator form of `solve`: yields after the launches of every LM iteration have been queued (before the
         host looks at the convergence flags), so that a driver can interleave several solvers on different streams
         (`solve_split`).  The result dict is left in `self.result`."""
         b, lib = self.b, self.lib
         S, N, dev = b.S, b.N, q0.device
-        q = q0.clone().contiguous()
-        b.lam_eq = torch.zeros(S, N, 26, dtype=torch.float64, device=dev)
-        b.lam_in = torch.zeros(S, N, self.m.n_ineq, dtype=torch.float64, device=dev)
+        if not hasattr(self, "_q_work"):
+            # work buffers of the loop, allocated once per solver: their addresses stay the same from solve to solve, which
+            # is what lets a captured iteration (graph=True) be replayed by later solves
+            f64 = dict(dtype=torch.float64, device=dev)
+            self._q_work = torch.empty(S, N, 54, **f64)
+            self._lam_eq = torch.empty(S, N, 26, **f64)
+            self._lam_in = torch.empty(S, N, self.m.n_ineq, **f64)
+            self._cost_try = torch.zeros(S, 4, **f64)
+            self._prior_try = torch.zeros(S, 2, **f64) if self.priors is not None else None
+            self._graphs = {}
+        q = self._q_work
+        q.copy_(q0)
+        b.lam_eq, b.lam_in = self._lam_eq.zero_(), self._lam_in.zero_()
         self.state.zero_()
         self.state[1].fill_(damp0)
         self.state[2].fill_(2.0)
         self.counters.zero_()
-        cost_try = torch.zeros(S, 4, dtype=torch.float64, device=dev)
-        prior_try = torch.zeros(S, 2, dtype=torch.float64, device=dev) if self.priors is not None else None
+        cost_try, prior_try = self._cost_try, self._prior_try
         damp = self.state[1]
         total_inner = 0
         ftols = tuple(ftol) if isinstance(ftol, (tuple, list)) else (ftol,)
@@ -418,7 +429,7 @@ class Solver:
             if self.priors is not None:
                 self.state[0].add_(self.prior_cost.sum(dim=1))
             self.active.fill_(1)
-            for it in range(max_iter):
+            def iteration():
                 b.active = self.active if skip_converged else None      # converged sequences cost nothing from here on
                 self.lm_step(q, damp)
                 self.evaluate(self.q_try, cost_out=cost_try, prior_out=prior_try)
@@ -435,6 +446,40 @@ class Solver:
                                                        _ptr(self.active), C.c_double(ftol), _stream()),
                                "cpe_step_accept_f64")
                 self.launches += 1
+
+            # graph=True: the launches of ONE iteration (K2, K3, K4, K1, reduce, K5 -- six to ten kernels whose arguments
+            # do not change while the penalty stays the same: every step size, damping and convergence flag lives in
+            # device memory) are captured into a CUDA graph and replayed; the very first iteration of a solver runs
+            # eagerly so that no module is loaded under capture.  Same kernels, same order, same arguments: results are
+            # bit-identical to the eager loop.
+            use_graph = graph and getattr(self, "k3_stream", None) is None
+            # every scalar and pointer the captured launches bake in: the batch struct itself (penalties, loss, pointers)
+            key = (bytes(b.struct()), ftol, bool(skip_converged)) if use_graph else None
+            for it in range(max_iter):
+                if not use_graph or not getattr(self, "_graph_warm", False):
+                    iteration()
+                    self._graph_warm = True
+                else:
+                    if key not in self._graphs:
+                        # captured once per (penalty, tolerance) of this solver and kept: later rounds with the same
+                        # penalty and later solves replay it.  Plain capture_begin / capture_end on a side stream
+                        # (torch.cuda.graph() would add a garbage collection and a device synchronisation per capture)
+                        l0 = self.launches
+                        g = torch.cuda.CUDAGraph()
+                        cur, side = torch.cuda.current_stream(), self._capture_stream()
+                        side.wait_stream(cur)
+                        with torch.cuda.stream(side):
+                            g.capture_begin()
+                            try:
+                                iteration()
+                            finally:
+                                g.capture_end()
+                        cur.wait_stream(side)
+                        self._graphs[key] = (g, self.launches - l0)
+                        self.launches = l0
+                    g, per_iter = self._graphs[key]
+                    g.replay()
+                    self.launches += per_iter
                 total_inner += 1
                 yield total_inner
                 if (it + 1) % check_every == 0 and not bool(self.active.any()):
@@ -446,11 +491,16 @@ class Solver:
                        "cpe_update_multipliers_f64")
             self.launches += 1
         out = self.evaluate(q, constraints=True)
-        res = dict(q=q, cost=out["cost"].clone(), c_eq=out["c_eq"], v_in=out["v_in"], counters=self.counters.clone(),
-                   status=self.exit_status(out), lockstep_iterations=total_inner)
+        res = dict(q=q.clone(), cost=out["cost"].clone(), c_eq=out["c_eq"].clone(), v_in=out["v_in"].clone(),
+                   counters=self.counters.clone(), status=self.exit_status(out), lockstep_iterations=total_inner)
         if self.priors is not None:
             res["prior_cost"] = out["prior_cost"].clone()
         self.result = res
+
+    def _capture_stream(self):
+        if not hasattr(self, "_cap_stream"):
+            self._cap_stream = torch.cuda.Stream(device=self.m.device)
+        return self._cap_stream
 
     def exit_status(self, out):
         """status[S] of CPE_STATUS_* flags from the final cost, the activity flags of the last round and K3's pivots."""

@@ -562,3 +562,22 @@ def test_host_evaluator_modes_match_the_resident_evaluation(gpu):
         assert h2d == 5 * 9 * 54 * 8 + (0 if resident else h_meas.numel() * h_meas.element_size())
         if resid_out:
             assert torch.equal(hev.h_resid, ref["resid"].cpu()) and d2h == 5 * 4 * 8 + ref["resid"].numel() * 8
+
+
+def test_graph_replay_of_the_lm_iteration_is_bit_identical(gpu):
+    """`Solver.solve(graph=True)`: the launches of one LM iteration captured per multiplier round into a CUDA graph and
+    replayed -- same kernels, order and arguments, so q, cost, counters and status equal the eager loop bit for bit
+    (ragged batch; a second solve on the same solver re-captures against its new buffers)."""
+    import torch
+    from cheetah_pose_estimation_b200 import engine, synthetic
+    prob = synthetic.make_problem(S=5, N=14, C=4, seed=52)
+    prob.n_frames[:] = (14, 9, 14, 4, 11)
+    q0 = torch.as_tensor(prob.q_init, device="cuda:0")
+    ref = engine.Solver(gpu, prob.to_batch("cuda:0")).solve(q0, max_iter=12, n_outer=3)
+    sv = engine.Solver(gpu, prob.to_batch("cuda:0"))
+    for _ in range(2):
+        res = sv.solve(q0, max_iter=12, n_outer=3, graph=True)
+        torch.cuda.synchronize()
+        for k in ("q", "cost", "counters", "status", "c_eq", "v_in"):
+            assert torch.equal(res[k], ref[k]), k
+        assert res["lockstep_iterations"] == ref["lockstep_iterations"]
