@@ -38,7 +38,7 @@ class CpeBatch(C.Structure):
         ("n_frames", c_i32p), ("h", c_f64p), ("meas", C.c_void_p), ("cams", c_f64p), ("chain_vec", c_f64p),
         ("lam_eq", c_f64p), ("lam_in", c_f64p), ("active", c_i32p),
         ("shutter_tau", c_f64p), ("base_dq", c_f64p), ("base_ddq", c_f64p),
-        ("n_cams", c_i32p),
+        ("n_cams", c_i32p), ("meas_gate", C.c_void_p),
     ]
 
 
@@ -100,6 +100,9 @@ EXPORTS = {
     "cpe_eom_slack_noalloc_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p, c_f64p, C.c_void_p]),
     "cpe_torque_costs_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, C.c_int32, c_f64p, c_f64p, c_f64p, c_f64p, c_f64p,
                                        C.c_void_p]),
+    "cpe_eval_host_uvg_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpeBatch), C.c_void_p, C.c_void_p, C.c_void_p, c_f64p,
+                                        C.c_void_p, C.c_void_p, C.POINTER(CpeEvalOut), c_f64p, C.c_void_p, C.c_void_p,
+                                        C.c_void_p]),
     "cpe_finalize_status_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, c_i32p, c_i32p, c_i32p, C.c_void_p]),
     "cpe_eval_host_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpeBatch), C.c_void_p, C.c_void_p, c_f64p,
                                     C.c_void_p, C.POINTER(CpeEvalOut), c_f64p, C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -151,15 +151,16 @@ __global__ void finalize_status_kernel(int S, const double *cost, const double *
     status[s] = st;
 }
 
-__global__ void update_multipliers_kernel(int S, int N, int n_ineq, const int32_t *n_frames, double mu_eq, double mu_in,
-                                          const double *c_eq, const double *v_in, double *lam_eq, double *lam_in) {
+__global__ void update_multipliers_kernel(int S, int N, int n_ineq, const int32_t *n_frames, const int32_t *active,
+                                          double mu_eq, double mu_in, const double *c_eq, const double *v_in,
+                                          double *lam_eq, double *lam_in) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     const size_t per = 26 + n_ineq;
     if (i >= (size_t)S * N * per) return;
     const size_t fidx = i / per;
     const int e = (int)(i - fidx * per);
     const int s = (int)(fidx / N), k = (int)(fidx - (size_t)s * N);
-    if (k >= n_frames[s]) return;
+    if (k >= n_frames[s] || (active && !active[s])) return;
     if (e < 26) lam_eq[fidx * 26 + e] += mu_eq * c_eq[fidx * 26 + e];
     else lam_in[fidx * n_ineq + e - 26] = mu_in * v_in[fidx * n_ineq + e - 26];
 }
@@ -218,7 +219,7 @@ extern "C" int cpe_update_multipliers_f64(const cpe_model *model, const cpe_batc
     if (!model || !b || !c_eq || !v_in || !lam_eq || !lam_in) return CPE_E_NULL;
     const size_t n = (size_t)b->S * b->N * (26 + model->n_ineq);
     cpe::update_multipliers_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-        b->S, b->N, model->n_ineq, b->n_frames, b->mu_eq, b->mu_in, c_eq, v_in, lam_eq, lam_in);
+        b->S, b->N, model->n_ineq, b->n_frames, b->active, b->mu_eq, b->mu_in, c_eq, v_in, lam_eq, lam_in);
     return (int)cudaGetLastError();
 }
 
@@ -229,6 +230,7 @@ extern "C" int cpe_eval_host_f64(const cpe_model *model, const cpe_batch *bd, co
     if (!out_dev->frame_cost || (h_meas && !d_meas) || (!h_meas && !bd->meas)) return CPE_E_NULL;
     cudaStream_t st = (cudaStream_t)stream;
     const size_t frames = (size_t)bd->S * bd->N;
+    if (bd->meas_layout == CPE_MEAS_F32X2G) return CPE_E_ARG;       // two arrays cross the bus: cpe_eval_host_uvg_f64
     const size_t rec = bd->meas_layout == CPE_MEAS_F64X4 ? 32 : (bd->meas_layout == CPE_MEAS_F32X3 ? 12 : 16);
     const size_t mbytes = frames * bd->C * 24 * bd->W * rec;
     cudaError_t e = cudaMemcpyAsync(d_q, h_q, frames * 54 * sizeof(double), cudaMemcpyHostToDevice, st);
@@ -248,6 +250,40 @@ extern "C" int cpe_eval_host_f64(const cpe_model *model, const cpe_batch *bd, co
     if (h_resid && out_dev->resid) {
         e = cudaMemcpyAsync(h_resid, out_dev->resid, frames * bd->C * 24 * bd->W * 2 * sizeof(double),
                             cudaMemcpyDeviceToHost, st);
+        if (e != cudaSuccess) return (int)e;
+    }
+    return 0;
+}
+
+extern "C" int cpe_eval_host_uvg_f64(const cpe_model *model, const cpe_batch *bd, const double *h_q, const void *h_uv,
+                                     const uint8_t *h_gate, double *d_q, void *d_uv, uint8_t *d_gate,
+                                     const cpe_eval_out *out_dev, double *d_cost, double *h_cost, double *h_resid,
+                                     void *stream) {
+    if (!model || !bd || !h_q || !d_q || !out_dev || !d_cost || !h_cost || !out_dev->frame_cost) return CPE_E_NULL;
+    if (bd->meas_layout != CPE_MEAS_F32X2G) return CPE_E_ARG;
+    if (h_uv ? (!h_gate || !d_uv || !d_gate) : (!bd->meas || !bd->meas_gate)) return CPE_E_NULL;
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t frames = (size_t)bd->S * bd->N;
+    const size_t recs = frames * bd->C * 24 * bd->W;
+    cudaError_t e = cudaMemcpyAsync(d_q, h_q, frames * 54 * sizeof(double), cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return (int)e;
+    cpe_batch b = *bd;
+    if (h_uv) {
+        e = cudaMemcpyAsync(d_uv, h_uv, recs * 2 * sizeof(float), cudaMemcpyHostToDevice, st);
+        if (e != cudaSuccess) return (int)e;
+        e = cudaMemcpyAsync(d_gate, h_gate, recs, cudaMemcpyHostToDevice, st);
+        if (e != cudaSuccess) return (int)e;
+        b.meas = d_uv;
+        b.meas_gate = d_gate;
+    }
+    int rc = cpe_eval_f64(model, &b, d_q, out_dev, stream);
+    if (rc) return rc;
+    rc = cpe_reduce_cost_f64(&b, out_dev->frame_cost, d_cost, stream);
+    if (rc) return rc;
+    e = cudaMemcpyAsync(h_cost, d_cost, (size_t)bd->S * 4 * sizeof(double), cudaMemcpyDeviceToHost, st);
+    if (e != cudaSuccess) return (int)e;
+    if (h_resid && out_dev->resid) {
+        e = cudaMemcpyAsync(h_resid, out_dev->resid, recs * 2 * sizeof(double), cudaMemcpyDeviceToHost, st);
         if (e != cudaSuccess) return (int)e;
     }
     return 0;

@@ -13,7 +13,7 @@ import torch
 from . import _lib, skeleton
 
 FISHEYE, PINHOLE = 0, 1
-MEAS_F32X4, MEAS_F64X4, MEAS_F32X3 = 0, 1, 2      # include/cpe.h CPE_MEAS_*
+MEAS_F32X4, MEAS_F64X4, MEAS_F32X3, MEAS_F32X2G = 0, 1, 2, 3      # include/cpe.h CPE_MEAS_*
 LOSS_REDESCENDING, LOSS_SQUARE = 0, 1             # include/cpe.h CPE_LOSS_*
 STATUS_PIVOT, STATUS_MAXITER, STATUS_NONFINITE = 1, 2, 4      # include/cpe.h CPE_STATUS_* (bit flags; 0 = converged)
 _I32_KEYS = ("chain_link", "eq_pairs", "ineq_idx", "ind_idx", "ind_pos", "grp_ndep", "grp_nnb", "grp_dep", "grp_nb",
@@ -87,9 +87,12 @@ class Batch:
     base_dq: torch.Tensor = None       # [S,N,3] f64
     base_ddq: torch.Tensor = None      # [S,N,3] f64
     n_cams: torch.Tensor = None        # [S] int32, optional: cameras c >= n_cams[s] are padding (ragged batch)
+    meas_gate: torch.Tensor = None     # [S,N,C,24,W] uint8: gates of the compact layout (meas = [..., 2] float32 u, v)
 
     @property
     def meas_layout(self):
+        if self.meas.shape[5] == 2:
+            return MEAS_F32X2G
         if self.meas.shape[5] == 3:
             return MEAS_F32X3
         return MEAS_F64X4 if self.meas.dtype == torch.float64 else MEAS_F32X4
@@ -115,7 +118,11 @@ class Batch:
             assert t.is_cuda and t.is_contiguous()
         assert self.n_frames.dtype == torch.int32 and self.h.dtype == torch.float64
         assert self.meas.dtype in (torch.float32, torch.float64) and self.meas.shape[3] == 24
-        assert self.meas.shape[5] == 4 or (self.meas.shape[5] == 3 and self.meas.dtype == torch.float32)
+        assert self.meas.shape[5] == 4 or (self.meas.shape[5] in (2, 3) and self.meas.dtype == torch.float32)
+        if self.meas.shape[5] == 2:
+            g = self.meas_gate
+            assert g is not None and g.is_cuda and g.is_contiguous() and g.dtype == torch.uint8
+            assert tuple(g.shape) == tuple(self.meas.shape[:5])
         assert self.cams.shape == (self.S, self.C, skeleton.CAM_STRIDE) and self.cams.dtype == torch.float64
         assert self.chain_vec.shape == (self.S, 24, 5, 3) and self.chain_vec.dtype == torch.float64
         b = _lib.CpeBatch()
@@ -131,6 +138,8 @@ class Batch:
         b.lam_eq = self.lam_eq.data_ptr() if self.lam_eq is not None else None
         b.lam_in = self.lam_in.data_ptr() if self.lam_in is not None else None
         b.active = self.active.data_ptr() if self.active is not None else None
+        if self.meas_gate is not None and self.meas.shape[5] == 2:
+            b.meas_gate = self.meas_gate.data_ptr()
         if self.n_cams is not None:
             assert self.n_cams.is_cuda and self.n_cams.dtype == torch.int32 and self.n_cams.shape == (self.S,)
             b.n_cams = self.n_cams.data_ptr()
@@ -155,7 +164,23 @@ class Batch:
                      shutter_tau=None if self.shutter_tau is None else self.shutter_tau[s0:s1],
                      base_dq=None if self.base_dq is None else self.base_dq[s0:s1],
                      base_ddq=None if self.base_ddq is None else self.base_ddq[s0:s1],
-                     n_cams=None if self.n_cams is None else self.n_cams[s0:s1])
+                     n_cams=None if self.n_cams is None else self.n_cams[s0:s1],
+                     meas_gate=None if self.meas_gate is None else self.meas_gate[s0:s1])
+
+    def compact(self):
+        """The same batch in the compact layout CPE_MEAS_F32X2G: float2 (u, v) records plus one gate byte each, the
+        likelihood test (strict >, acinoset_misc.py:231; NaN -> 0) done here once.  9 bytes per detection."""
+        m = self.meas
+        if m.shape[5] == 2:
+            return self
+        uv = m[..., 0:2].to(torch.float32)
+        fin = ~torch.isnan(uv).any(dim=-1)                     # the device gate of the DLC-native layout (meas_unpack)
+        gate = (m[..., 2].double() > float(self.dlc_thresh)) if m.shape[5] == 3 else (m[..., 2] != 0)
+        gate = (gate & fin).to(torch.uint8).contiguous()
+        uv = torch.where(fin[..., None], uv, torch.zeros_like(uv)).contiguous()
+        out = self.window(0, self.S)
+        out.meas, out.meas_gate = uv, gate
+        return out
 
     @staticmethod
     def from_numpy(meas, cams, chain_vec, h, n_frames=None, device="cuda", cam_model=FISHEYE, meas_dtype=torch.float32,
@@ -394,10 +419,15 @@ class Solver:
         return self.result
 
     def solve_steps(self, q0, max_iter=40, n_outer=4, damp0=1e-3, ftol=1e-6, mu_schedule=MU_SCHEDULE,
-                    check_every=4, skip_converged=True, graph=False):
+                    check_every=4, skip_converged=True, graph=False, extra_outer=0, feas_tol=(5e-5, 2.5e-4)):
         """Generator form of `solve`: yields after the launches of every LM iteration have been queued (before the
         host looks at the convergence flags), so that a driver can interleave several solvers on different streams
-        (`solve_split`).  The result dict is left in `self.result`."""
+        (`solve_split`).  The result dict is left in `self.result`.
+
+        extra_outer > 0: after the n_outer scheduled rounds, up to that many further rounds at the last penalty for the
+        sequences whose joint equalities / inequality rows still exceed feas_tol = (|c_eq|, |v_in|) -- IPOPT keeps going
+        until its constraint tolerance is met; a fixed round count does not.  Every other sequence is inactive in those
+        rounds (no step, no multiplier update), so its result is bit-identical to a solve without them."""
         b, lib = self.b, self.lib
         S, N, dev = b.S, b.N, q0.device
         if not hasattr(self, "_q_work"):
@@ -421,16 +451,34 @@ class Solver:
         damp = self.state[1]
         total_inner = 0
         ftols = tuple(ftol) if isinstance(ftol, (tuple, list)) else (ftol,)
-        for outer in range(n_outer):
+        need = held = None
+        extra_rounds = 0
+        for outer in range(n_outer + extra_outer):
+            if outer >= n_outer:
+                # self.c_eq / self.v_in hold the constraints at q (evaluated when the previous round ended)
+                need = ((self.c_eq.abs().amax(dim=(1, 2)) >= feas_tol[0])
+                        | (self.v_in.abs().amax(dim=(1, 2)) >= feas_tol[1])).to(torch.int32)
+                if not bool(need.any()):
+                    need = None
+                    break
+                if held is None:
+                    held = self.active.clone()                  # MAXITER flags of the last scheduled round
+                    ever = torch.zeros_like(need)
+                ever |= need
+                extra_rounds += 1
             b.mu_eq = b.mu_in = float(mu_schedule[min(outer, len(mu_schedule) - 1)])
             ftol = float(ftols[min(outer, len(ftols) - 1)])      # inexact inner solves while the multipliers are rough
             self.evaluate(q)
             self.state[0].copy_(self.cost.sum(dim=1))
             if self.priors is not None:
                 self.state[0].add_(self.prior_cost.sum(dim=1))
-            self.active.fill_(1)
+            if need is None:
+                self.active.fill_(1)
+            else:
+                self.active.copy_(need)
+            masked = skip_converged or need is not None
             def iteration():
-                b.active = self.active if skip_converged else None      # converged sequences cost nothing from here on
+                b.active = self.active if masked else None      # converged sequences cost nothing from here on
                 self.lm_step(q, damp)
                 self.evaluate(self.q_try, cost_out=cost_try, prior_out=prior_try)
                 b.active = None
@@ -454,7 +502,7 @@ class Solver:
             # bit-identical to the eager loop.
             use_graph = graph and getattr(self, "k3_stream", None) is None
             # every scalar and pointer the captured launches bake in: the batch struct itself (penalties, loss, pointers)
-            key = (bytes(b.struct()), ftol, bool(skip_converged)) if use_graph else None
+            key = (bytes(b.struct()), ftol, bool(masked)) if use_graph else None
             for it in range(max_iter):
                 if not use_graph or not getattr(self, "_graph_warm", False):
                     iteration()
@@ -485,11 +533,17 @@ class Solver:
                 if (it + 1) % check_every == 0 and not bool(self.active.any()):
                     break
             self.evaluate(q, constraints=True)
+            b.active = need                                     # extra rounds: only the sequences they ran for
             bs = b.struct()
+            b.active = None
             _lib.check(lib.cpe_update_multipliers_f64(C.byref(self.m.struct), C.byref(bs), _ptr(self.c_eq), _ptr(self.v_in),
                                                       _ptr(b.lam_eq), _ptr(b.lam_in), _stream()),
                        "cpe_update_multipliers_f64")
             self.launches += 1
+        if held is not None:
+            # sequences that sat out the extra rounds keep the activity (= MAXITER) flag of their own last round
+            self.active.copy_(torch.where(ever != 0, self.active, held))
+        self.extra_rounds = extra_rounds
         out = self.evaluate(q, constraints=True)
         res = dict(q=q.clone(), cost=out["cost"].clone(), c_eq=out["c_eq"].clone(), v_in=out["v_in"].clone(),
                    counters=self.counters.clone(), status=self.exit_status(out), lockstep_iterations=total_inner)
@@ -717,6 +771,7 @@ class HostEvaluator:
         self.m, self.lib, self.proto = model, model.lib, proto
         self.S, self.wave, self.N, self.C, self.W = S, wave, proto.N, proto.C, proto.W
         self.resident_meas, self.resid_out = resident_meas, resid_out
+        self.compact = proto.meas.shape[5] == 2          # CPE_MEAS_F32X2G: float2 (u, v) + gate byte (cpe_eval_host_uvg_f64)
         dev = model.device
         f64 = dict(dtype=torch.float64, device=dev)
         self.streams = [torch.cuda.Stream(device=dev) for _ in range(2)]
@@ -725,6 +780,8 @@ class HostEvaluator:
             st = dict(q=torch.empty(wave, self.N, 54, **f64),
                       meas=None if resident_meas else torch.empty(wave, self.N, self.C, 24, self.W, proto.meas.shape[5],
                                                                   dtype=proto.meas.dtype, device=dev),
+                      gate=torch.empty(wave, self.N, self.C, 24, self.W, dtype=torch.uint8, device=dev)
+                      if (self.compact and not resident_meas) else None,
                       frame_cost=torch.zeros(wave, self.N, 4, **f64), cost=torch.zeros(wave, 4, **f64),
                       jac=torch.empty(wave, self.N, self.C, model.jac_width, **f64) if jac else None,
                       resid=torch.empty(wave, self.N, self.C, 24, self.W, 2, **f64) if resid_out else None)
@@ -734,18 +791,21 @@ class HostEvaluator:
         self.launches = 0
 
     def bytes_per_call(self):
-        mb = 0 if self.resident_meas else self.C * 24 * self.W * self.proto.meas.shape[5] * self.proto.meas.element_size()
+        mb = 0 if self.resident_meas else self.C * 24 * self.W * (
+            self.proto.meas.shape[5] * self.proto.meas.element_size() + (1 if self.compact else 0))
         h2d = self.S * self.N * (54 * 8 + mb)
         d2h = self.S * 4 * 8 + (self.S * self.N * self.C * 24 * self.W * 2 * 8 if self.resid_out else 0)
         return h2d, d2h
 
-    def __call__(self, h_q, h_meas=None):
-        """h_q[S,N,54] f64 (and, unless resident_meas, h_meas[S,N,C,24,W,4|3]) pinned host tensors -> pinned cost[S,4]
-        (valid after return; `self.h_resid` holds the residuals with resid_out)."""
+    def __call__(self, h_q, h_meas=None, h_gate=None):
+        """h_q[S,N,54] f64 (and, unless resident_meas, h_meas[S,N,C,24,W,4|3|2] -- with h_gate[S,N,C,24,W] uint8 for the
+        compact layout) pinned host tensors -> pinned cost[S,4] (valid after return; `self.h_resid` holds the residuals
+        with resid_out)."""
         assert not h_q.is_cuda and h_q.is_pinned()
         assert self.resident_meas == (h_meas is None)
         if h_meas is not None:
             assert not h_meas.is_cuda and h_meas.is_pinned()
+            assert (h_gate is not None and h_gate.is_pinned() and h_gate.dtype == torch.uint8) == self.compact
         cur = torch.cuda.current_stream()
         for st in self.streams:
             st.wait_stream(cur)
@@ -760,12 +820,20 @@ class HostEvaluator:
                 eo.jac = stg["jac"].data_ptr()
             if stg["resid"] is not None:
                 eo.resid = stg["resid"].data_ptr()
-            _lib.check(self.lib.cpe_eval_host_f64(
-                C.byref(self.m.struct), C.byref(bs), C.c_void_p(h_q[s0:s1].data_ptr()),
-                None if h_meas is None else C.c_void_p(h_meas[s0:s1].data_ptr()), _ptr(stg["q"]), _ptr(stg["meas"]),
-                C.byref(eo), _ptr(stg["cost"]), C.c_void_p(self.h_cost[s0:s1].data_ptr()),
-                None if self.h_resid is None else C.c_void_p(self.h_resid[s0:s1].data_ptr()),
-                C.c_void_p(stream.cuda_stream)), "cpe_eval_host_f64")
+            hr = None if self.h_resid is None else C.c_void_p(self.h_resid[s0:s1].data_ptr())
+            if self.compact:
+                _lib.check(self.lib.cpe_eval_host_uvg_f64(
+                    C.byref(self.m.struct), C.byref(bs), C.c_void_p(h_q[s0:s1].data_ptr()),
+                    None if h_meas is None else C.c_void_p(h_meas[s0:s1].data_ptr()),
+                    None if h_gate is None else C.c_void_p(h_gate[s0:s1].data_ptr()), _ptr(stg["q"]), _ptr(stg["meas"]),
+                    _ptr(stg["gate"]), C.byref(eo), _ptr(stg["cost"]), C.c_void_p(self.h_cost[s0:s1].data_ptr()), hr,
+                    C.c_void_p(stream.cuda_stream)), "cpe_eval_host_uvg_f64")
+            else:
+                _lib.check(self.lib.cpe_eval_host_f64(
+                    C.byref(self.m.struct), C.byref(bs), C.c_void_p(h_q[s0:s1].data_ptr()),
+                    None if h_meas is None else C.c_void_p(h_meas[s0:s1].data_ptr()), _ptr(stg["q"]), _ptr(stg["meas"]),
+                    C.byref(eo), _ptr(stg["cost"]), C.c_void_p(self.h_cost[s0:s1].data_ptr()), hr,
+                    C.c_void_p(stream.cuda_stream)), "cpe_eval_host_f64")
             self.launches += 2
         for st in self.streams:
             cur.wait_stream(st)

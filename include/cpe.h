@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 116          /* 0.1.16 */
+#define CPE_VERSION 117          /* 0.1.17 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -62,6 +62,10 @@ extern "C" {
 #define CPE_MEAS_F64X4 1         /* double4 {u, v, gate, unused} */
 #define CPE_MEAS_F32X3 2         /* float3  {x, y, likelihood}: the DLC-native triple (acinoset_misc.py:237-256); the
                                     strict test likelihood > dlc_thresh (acinoset_misc.py:231) runs on the device */
+
+#define CPE_MEAS_F32X2G 3        /* float2 {u, v} in cpe_batch.meas plus one byte per record in cpe_batch.meas_gate (0 / 1,
+                                    the likelihood test done once on the host): 9 bytes per detection instead of 12 / 16 --
+                                    the layout of choice when the detections cross PCIe (cpe_eval_host_uvg_f64) */
 
 #define CPE_LOSS_REDESCENDING 0  /* acinoset_misc.py:476-482, 2001-2015 */
 #define CPE_LOSS_SQUARE 1        /* hand-labelled data: (w slack)^2, camera multiplier not applied (acinoset_misc.py:471-474) */
@@ -161,6 +165,7 @@ typedef struct cpe_batch {
        the real cameras every sum keeps the order of the unpadded problem: results are bit-identical to a batch with
        C = n_cams[s].  The padded cams[] rows must still hold a valid camera.  NULL = C cameras for every sequence. */
     const int32_t *n_cams;          /* [S] optional */
+    const uint8_t *meas_gate;       /* [S,N,C,24,W] gates of CPE_MEAS_F32X2G (NULL for the other layouts) */
 } cpe_batch;
 
 /* Optional outputs of cpe_eval (NULL = skip). */
@@ -298,7 +303,8 @@ int cpe_band_solve_general_f64(const cpe_batch *batch, const double *Sblk, const
 int cpe_finalize_status_f64(const cpe_batch *batch, const double *cost, const double *cost_extra, const int32_t *active,
                             const int32_t *pivot, int32_t *status, void *stream);
 
-/* Augmented-Lagrangian multiplier update: lam_eq += mu_eq * c_eq ; lam_in = mu_in * v_in. */
+/* Augmented-Lagrangian multiplier update: lam_eq += mu_eq * c_eq ; lam_in = mu_in * v_in.  Sequences with
+ * batch->active[s] == 0 keep their multipliers (NULL: all are updated). */
 int cpe_update_multipliers_f64(const cpe_model *model, const cpe_batch *batch, const double *c_eq,
                                const double *v_in, double *lam_eq, double *lam_in, void *stream);
 
@@ -330,6 +336,13 @@ int cpe_eom_affine_f64(const cpe_batch *batch, const double *q, const double *dq
  * optimum value to ~1e-14 ||a|| on the fixture).  grf[S,N,20], resid[S,N] = the optimal || eom ||. */
 int cpe_grf_solve_f64(const cpe_batch *batch, const double *a, const double *Bm, const int32_t *contact, int32_t iters,
                       double *grf, double *resid, void *stream);
+
+/* The same for the compact layout CPE_MEAS_F32X2G: h_uv / d_uv hold float2 {u, v} records, h_gate / d_gate one byte each
+ * (9 bytes per detection over PCIe instead of 12).  batch_dev->meas_layout must be CPE_MEAS_F32X2G; h_uv == NULL means the
+ * detections are already resident in batch_dev->meas / meas_gate. */
+int cpe_eval_host_uvg_f64(const cpe_model *model, const cpe_batch *batch_dev, const double *h_q, const void *h_uv,
+                          const uint8_t *h_gate, double *d_q, void *d_uv, uint8_t *d_gate, const cpe_eval_out *out_dev,
+                          double *d_cost, double *h_cost, double *h_resid, void *stream);
 
 /* Trajectory-level cost terms of the kinetic objective (acinoset_opt.py:905-921), each with its gradient.  Frame ranges
  * follow the reference's code (1-based `fe < nfe - 2` / `fe < nfe - 1`: one term fewer than the data allows).

@@ -323,6 +323,62 @@ def test_dlc_native_layout_equals_pregated(gpu):
     assert torch.equal(d3, d4)
 
 
+def test_compact_layout_equals_dlc_native_and_pregated(gpu):
+    """CPE_MEAS_F32X2G (float2 u, v + one gate byte, 9 B per detection; the likelihood / NaN test done once by
+    Batch.compact) against the DLC-native float3 and the host-gated float4 records: costs, residuals, Jacobians, the
+    normal equations' LM step and a whole solve are bit-identical; NaN detections and the exact-threshold case included;
+    W = 3 (pairwise layout) as well."""
+    import torch
+    from cheetah_pose_estimation_b200 import engine
+    prob, batch, solver, q, qd = _setup(gpu, S=3, N=8, C=6, seed=31)
+    rng = np.random.default_rng(4)
+    for W in (1, 3):
+        meas = np.repeat(prob.meas, W, axis=4) if W > 1 else prob.meas
+        lik = rng.random(meas.shape[:-1]).astype(np.float32)
+        lik[0, 0, 0, :4, 0] = 0.5                                            # exactly at the threshold: gate off
+        m3 = np.concatenate([meas[..., 0:2], lik[..., None]], -1).astype(np.float32)
+        m3[1, 2, 1, 5, 0, 0] = np.nan                                        # NaN coordinate: gate off, finite stand-in
+        m3[2, 3, 4, 7, 0, 2] = np.nan                                        # NaN likelihood: gate off
+        b3 = engine.Batch.from_numpy(m3, prob.cams, prob.chain_vec, prob.h, dlc_native=True)
+        b2 = b3.compact()
+        assert b2.meas_layout == engine.MEAS_F32X2G and b2.meas.shape[-1] == 2 and b2.meas_gate.dtype == torch.uint8
+        assert b2.compact() is b2
+        m4 = np.zeros(meas.shape[:-1] + (4,), np.float32)
+        m4[..., 0:2] = np.where(np.isnan(m3[..., 0:2]).any(-1, keepdims=True), 0.0, m3[..., 0:2])
+        with np.errstate(invalid="ignore"):
+            m4[..., 2] = ((m3[..., 2].astype(np.float64) > 0.5) & ~np.isnan(m3[..., 0:2]).any(-1)).astype(np.float32)
+        b4 = engine.Batch.from_numpy(m4, prob.cams, prob.chain_vec, prob.h)
+        assert np.array_equal(b2.meas_gate.cpu().numpy(), m4[..., 2].astype(np.uint8))
+        assert int(b2.meas_gate[1, 2, 1, 5, 0]) == 0 and int(b2.meas_gate[2, 3, 4, 7, 0]) == 0
+        s2, s3, s4 = (engine.Solver(gpu, b) for b in (b2, b3, b4))
+        o2, o3, o4 = (s.evaluate(qd, resid=True, jac=True) for s in (s2, s3, s4))
+        for k in ("cost", "resid", "jac"):
+            assert torch.equal(o2[k], o3[k]), (W, k, "compact vs DLC-native")
+            assert torch.equal(o2[k], o4[k]), (W, k, "compact vs host-gated float4")
+        assert bool(torch.isfinite(o2["cost"]).all())
+        damp = torch.full((3,), 1e-2, dtype=torch.float64, device="cuda:0")
+        d2, d3 = s2.lm_step(qd, damp)[0].clone(), s3.lm_step(qd, damp)[0].clone()
+        assert torch.equal(d2, d3), W
+        q0 = torch.as_tensor(prob.q_init, device="cuda:0")
+        r2, r3 = s2.solve(q0, max_iter=8, n_outer=2), s3.solve(q0, max_iter=8, n_outer=2)
+        for k in ("q", "cost", "counters", "status"):
+            assert torch.equal(r2[k], r3[k]), (W, k)
+    # the f32 flavour reads the same records
+    o2, o3 = s2.evaluate(qd, resid=True, jac=True, f32=True), s3.evaluate(qd, resid=True, jac=True, f32=True)
+    for k in ("cost", "resid", "jac"):
+        assert torch.equal(o2[k], o3[k]), k
+    # a compact batch without its gate array is refused at the boundary
+    import ctypes as C
+    from cheetah_pose_estimation_b200 import _lib
+    bs = b2.struct()
+    bs.meas_gate = None
+    eo = _lib.CpeEvalOut()
+    fc = torch.zeros(3, 8, 4, dtype=torch.float64, device="cuda:0")
+    eo.frame_cost = fc.data_ptr()
+    rc = gpu.lib.cpe_eval_f64(C.byref(gpu.struct), C.byref(bs), C.c_void_p(qd.data_ptr()), C.byref(eo), None)
+    assert rc == -3                                                          # CPE_E_NULL
+
+
 def test_skipping_converged_sequences_changes_nothing(gpu):
     """cpe_batch.active: sequences that converged are skipped by every kernel; results must be bit-identical."""
     import torch
@@ -562,6 +618,17 @@ def test_host_evaluator_modes_match_the_resident_evaluation(gpu):
         assert h2d == 5 * 9 * 54 * 8 + (0 if resident else h_meas.numel() * h_meas.element_size())
         if resid_out:
             assert torch.equal(hev.h_resid, ref["resid"].cpu()) and d2h == 5 * 4 * 8 + ref["resid"].numel() * 8
+    # the compact layout through its own entry point (cpe_eval_host_uvg_f64): float2 records + gate bytes cross the bus
+    cb = batch.compact()
+    h_uv, h_gate = cb.meas.cpu().pin_memory(), cb.meas_gate.cpu().pin_memory()
+    for resident, resid_out in ((False, False), (True, False), (False, True)):
+        hev = engine.HostEvaluator(gpu, cb, 5, 3, resident_meas=resident, resid_out=resid_out)
+        cost = hev(h_q, None if resident else h_uv, None if resident else h_gate)
+        assert torch.equal(cost, ref["cost"].cpu())
+        h2d, _ = hev.bytes_per_call()
+        assert h2d == 5 * 9 * 54 * 8 + (0 if resident else h_gate.numel() * 9)
+        if resid_out:
+            assert torch.equal(hev.h_resid, ref["resid"].cpu())
 
 
 def test_graph_replay_of_the_lm_iteration_is_bit_identical(gpu):
@@ -581,3 +648,33 @@ def test_graph_replay_of_the_lm_iteration_is_bit_identical(gpu):
         for k in ("q", "cost", "counters", "status", "c_eq", "v_in"):
             assert torch.equal(res[k], ref[k]), k
         assert res["lockstep_iterations"] == ref["lockstep_iterations"]
+
+
+def test_extra_rounds_only_touch_sequences_that_are_not_yet_feasible(gpu):
+    """`solve(extra_outer=k, feas_tol=...)`: after the scheduled multiplier rounds, further rounds run for the sequences
+    whose constraints still exceed feas_tol and for nobody else.  With a schedule that is cut short (2 rounds) and a
+    tolerance between the violations of the batch, the sequences already below it come out bit-identical to the plain
+    solve and the others end below the tolerance (or at least strictly better)."""
+    import torch
+    from cheetah_pose_estimation_b200 import engine, synthetic
+    prob = synthetic.make_problem(S=6, N=14, C=4, seed=61)
+    prob.n_frames[:] = (14, 9, 14, 6, 11, 14)
+    q0 = torch.as_tensor(prob.q_init, device="cuda:0")
+    kw = dict(max_iter=12, n_outer=2, mu_schedule=(1e4, 1e5))             # the extra rounds stay at the last penalty
+    base = engine.Solver(gpu, prob.to_batch("cuda:0")).solve(q0, **kw)
+    viol = base["c_eq"].abs().amax(dim=(1, 2))
+    tol = float(viol.sort().values[2:4].mean())                          # three sequences below, three above
+    sv = engine.Solver(gpu, prob.to_batch("cuda:0"))
+    res = sv.solve(q0, extra_outer=6, feas_tol=(tol, 1.0), **kw)
+    torch.cuda.synchronize()
+    ok = viol < tol
+    assert int(ok.sum()) == 3 and 1 <= sv.extra_rounds <= 6
+    for k in ("q", "cost", "c_eq", "v_in", "counters", "status"):
+        assert torch.equal(res[k][ok], base[k][ok]), k
+    after = res["c_eq"].abs().amax(dim=(1, 2))
+    assert bool((after[~ok] < viol[~ok]).all()) and bool((res["counters"][~ok, 0] > base["counters"][~ok, 0]).all())
+    assert bool((after[~ok] < tol).all()) or sv.extra_rounds == 6
+    # nothing to do: no extra round runs and the result is the plain one
+    sv2 = engine.Solver(gpu, prob.to_batch("cuda:0"))
+    res2 = sv2.solve(q0, extra_outer=6, feas_tol=(1.0, 1.0), **kw)
+    assert sv2.extra_rounds == 0 and all(torch.equal(res2[k], base[k]) for k in ("q", "cost", "status"))
