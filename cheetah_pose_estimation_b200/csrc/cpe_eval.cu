@@ -374,8 +374,8 @@ static int launch_eval(const cpe_model *model, const cpe_batch *b, const double 
     if (!model || !b || !q || !eo) return CPE_E_NULL;
     if (b->S <= 0 || b->N <= 0 || b->C <= 0 || b->C > CPE_MAX_CAMS || (b->W != 1 && b->W != 3)) return CPE_E_DIM;
     if (model->n_ineq > CPE_MAX_INEQ || model->n_u <= 0 || model->n_u > 240 || model->n_u % 3) return CPE_E_DIM;
-    if (b->meas_layout < 0 || b->meas_layout > CPE_MEAS_F32X2G) return CPE_E_ARG;
-    if (b->meas_layout == CPE_MEAS_F32X2G && !b->meas_gate) return CPE_E_NULL;
+    if (b->meas_layout < 0 || b->meas_layout > CPE_MEAS_F32X2B) return CPE_E_ARG;
+    if (b->meas_layout >= CPE_MEAS_F32X2G && !b->meas_gate) return CPE_E_NULL;
     if (!b->meas || !b->cams || !b->chain_vec || !b->n_frames || !b->h) return CPE_E_NULL;
     if (!model->u_off || !model->u_item) return CPE_E_NULL;
     if ((b->shutter_tau || b->base_dq || b->base_ddq) && !(b->shutter_tau && b->base_dq && b->base_ddq)) return CPE_E_NULL;

@@ -81,6 +81,9 @@ __device__ __forceinline__ void meas_fetch(const cpe_batch &b, size_t idx, MeasR
     } else if (b.meas_layout == CPE_MEAS_F32X2G) {         // float2 {u, v} + gate byte
         const float2 uv = __ldg(reinterpret_cast<const float2 *>(b.meas) + idx);
         m.f.x = uv.x; m.f.y = uv.y; m.f.z = (float)__ldg(b.meas_gate + idx);
+    } else if (b.meas_layout == CPE_MEAS_F32X2B) {         // float2 {u, v} + gate bit
+        const float2 uv = __ldg(reinterpret_cast<const float2 *>(b.meas) + idx);
+        m.f.x = uv.x; m.f.y = uv.y; m.f.z = (float)((__ldg(b.meas_gate + (idx >> 3)) >> (idx & 7)) & 1);
     } else {                                   // CPE_MEAS_F32X3: DLC-native (x, y, likelihood)
         const float *f = reinterpret_cast<const float *>(b.meas) + 3 * idx;
         m.f.x = __ldg(f); m.f.y = __ldg(f + 1); m.f.z = __ldg(f + 2);
@@ -94,7 +97,7 @@ __device__ __forceinline__ void meas_unpack(const cpe_batch &b, const MeasRaw &m
         u = m.d.x; v = m.d.y; gate = m.d.z;
     } else {
         u = (double)m.f.x; v = (double)m.f.y;
-        if (b.meas_layout == CPE_MEAS_F32X4 || b.meas_layout == CPE_MEAS_F32X2G) {
+        if (b.meas_layout != CPE_MEAS_F32X3) {
             gate = (double)m.f.z;
         } else {
             // DLC-native record, gated here: a NaN coordinate or likelihood gets gate 0 and a finite stand-in, so that it

@@ -230,7 +230,7 @@ extern "C" int cpe_eval_host_f64(const cpe_model *model, const cpe_batch *bd, co
     if (!out_dev->frame_cost || (h_meas && !d_meas) || (!h_meas && !bd->meas)) return CPE_E_NULL;
     cudaStream_t st = (cudaStream_t)stream;
     const size_t frames = (size_t)bd->S * bd->N;
-    if (bd->meas_layout == CPE_MEAS_F32X2G) return CPE_E_ARG;       // two arrays cross the bus: cpe_eval_host_uvg_f64
+    if (bd->meas_layout >= CPE_MEAS_F32X2G) return CPE_E_ARG;       // two arrays cross the bus: cpe_eval_host_uvg_f64
     const size_t rec = bd->meas_layout == CPE_MEAS_F64X4 ? 32 : (bd->meas_layout == CPE_MEAS_F32X3 ? 12 : 16);
     const size_t mbytes = frames * bd->C * 24 * bd->W * rec;
     cudaError_t e = cudaMemcpyAsync(d_q, h_q, frames * 54 * sizeof(double), cudaMemcpyHostToDevice, st);
@@ -260,7 +260,7 @@ extern "C" int cpe_eval_host_uvg_f64(const cpe_model *model, const cpe_batch *bd
                                      const cpe_eval_out *out_dev, double *d_cost, double *h_cost, double *h_resid,
                                      void *stream) {
     if (!model || !bd || !h_q || !d_q || !out_dev || !d_cost || !h_cost || !out_dev->frame_cost) return CPE_E_NULL;
-    if (bd->meas_layout != CPE_MEAS_F32X2G) return CPE_E_ARG;
+    if (bd->meas_layout != CPE_MEAS_F32X2G && bd->meas_layout != CPE_MEAS_F32X2B) return CPE_E_ARG;
     if (h_uv ? (!h_gate || !d_uv || !d_gate) : (!bd->meas || !bd->meas_gate)) return CPE_E_NULL;
     cudaStream_t st = (cudaStream_t)stream;
     const size_t frames = (size_t)bd->S * bd->N;
@@ -271,7 +271,7 @@ extern "C" int cpe_eval_host_uvg_f64(const cpe_model *model, const cpe_batch *bd
     if (h_uv) {
         e = cudaMemcpyAsync(d_uv, h_uv, recs * 2 * sizeof(float), cudaMemcpyHostToDevice, st);
         if (e != cudaSuccess) return (int)e;
-        e = cudaMemcpyAsync(d_gate, h_gate, recs, cudaMemcpyHostToDevice, st);
+        e = cudaMemcpyAsync(d_gate, h_gate, bd->meas_layout == CPE_MEAS_F32X2B ? (recs + 7) / 8 : recs, cudaMemcpyHostToDevice, st);
         if (e != cudaSuccess) return (int)e;
         b.meas = d_uv;
         b.meas_gate = d_gate;

@@ -13,7 +13,7 @@ import torch
 from . import _lib, skeleton
 
 FISHEYE, PINHOLE = 0, 1
-MEAS_F32X4, MEAS_F64X4, MEAS_F32X3, MEAS_F32X2G = 0, 1, 2, 3      # include/cpe.h CPE_MEAS_*
+MEAS_F32X4, MEAS_F64X4, MEAS_F32X3, MEAS_F32X2G, MEAS_F32X2B = 0, 1, 2, 3, 4      # include/cpe.h CPE_MEAS_*
 LOSS_REDESCENDING, LOSS_SQUARE = 0, 1             # include/cpe.h CPE_LOSS_*
 STATUS_PIVOT, STATUS_MAXITER, STATUS_NONFINITE = 1, 2, 4      # include/cpe.h CPE_STATUS_* (bit flags; 0 = converged)
 _I32_KEYS = ("chain_link", "eq_pairs", "ineq_idx", "ind_idx", "ind_pos", "grp_ndep", "grp_nnb", "grp_dep", "grp_nb",
@@ -64,6 +64,14 @@ class Model:
         self.struct = s
 
 
+def _pack_bits(gate):
+    """[S, ...] uint8 0 / 1 -> [S, n / 8] uint8, bit (i & 7) of byte i >> 3 = gate i (numpy.packbits, bitorder little)."""
+    S = gate.shape[0]
+    g = gate.reshape(S, -1, 8).to(torch.int32)
+    w = torch.tensor([1, 2, 4, 8, 16, 32, 64, 128], dtype=torch.int32, device=gate.device)
+    return (g * w).sum(dim=2).to(torch.uint8).contiguous()
+
+
 @dataclass
 class Batch:
     """Device-resident inputs of S sequences (`cpe_batch`)."""
@@ -87,12 +95,13 @@ class Batch:
     base_dq: torch.Tensor = None       # [S,N,3] f64
     base_ddq: torch.Tensor = None      # [S,N,3] f64
     n_cams: torch.Tensor = None        # [S] int32, optional: cameras c >= n_cams[s] are padding (ragged batch)
-    meas_gate: torch.Tensor = None     # [S,N,C,24,W] uint8: gates of the compact layout (meas = [..., 2] float32 u, v)
+    meas_gate: torch.Tensor = None     # [S,N,C,24,W] uint8: gates of the compact layout (meas = [..., 2] float32 u, v), or
+                                       # [S, N*C*24*W/8] uint8: the same packed 8 per byte (little-endian bit order)
 
     @property
     def meas_layout(self):
         if self.meas.shape[5] == 2:
-            return MEAS_F32X2G
+            return MEAS_F32X2B if self.meas_gate.dim() == 2 else MEAS_F32X2G
         if self.meas.shape[5] == 3:
             return MEAS_F32X3
         return MEAS_F64X4 if self.meas.dtype == torch.float64 else MEAS_F32X4
@@ -122,7 +131,7 @@ class Batch:
         if self.meas.shape[5] == 2:
             g = self.meas_gate
             assert g is not None and g.is_cuda and g.is_contiguous() and g.dtype == torch.uint8
-            assert tuple(g.shape) == tuple(self.meas.shape[:5])
+            assert tuple(g.shape) in (tuple(self.meas.shape[:5]), (self.S, self.N * self.C * 24 * self.W // 8))
         assert self.cams.shape == (self.S, self.C, skeleton.CAM_STRIDE) and self.cams.dtype == torch.float64
         assert self.chain_vec.shape == (self.S, 24, 5, 3) and self.chain_vec.dtype == torch.float64
         b = _lib.CpeBatch()
@@ -167,11 +176,17 @@ class Batch:
                      n_cams=None if self.n_cams is None else self.n_cams[s0:s1],
                      meas_gate=None if self.meas_gate is None else self.meas_gate[s0:s1])
 
-    def compact(self):
+    def compact(self, bits=False):
         """The same batch in the compact layout CPE_MEAS_F32X2G: float2 (u, v) records plus one gate byte each, the
-        likelihood test (strict >, acinoset_misc.py:231; NaN -> 0) done here once.  9 bytes per detection."""
+        likelihood test (strict >, acinoset_misc.py:231; NaN -> 0) done here once.  9 bytes per detection; with
+        `bits` the gates are packed 8 per byte (CPE_MEAS_F32X2B, 8.125 bytes per detection)."""
         m = self.meas
         if m.shape[5] == 2:
+            if bits and self.meas_gate.dim() != 2:
+                out = self.window(0, self.S)
+                out.meas_gate = _pack_bits(self.meas_gate)
+                return out
+            assert bits == (self.meas_gate.dim() == 2)
             return self
         uv = m[..., 0:2].to(torch.float32)
         fin = ~torch.isnan(uv).any(dim=-1)                     # the device gate of the DLC-native layout (meas_unpack)
@@ -179,7 +194,7 @@ class Batch:
         gate = (gate & fin).to(torch.uint8).contiguous()
         uv = torch.where(fin[..., None], uv, torch.zeros_like(uv)).contiguous()
         out = self.window(0, self.S)
-        out.meas, out.meas_gate = uv, gate
+        out.meas, out.meas_gate = uv, (_pack_bits(gate) if bits else gate)
         return out
 
     @staticmethod
@@ -771,7 +786,9 @@ class HostEvaluator:
         self.m, self.lib, self.proto = model, model.lib, proto
         self.S, self.wave, self.N, self.C, self.W = S, wave, proto.N, proto.C, proto.W
         self.resident_meas, self.resid_out = resident_meas, resid_out
-        self.compact = proto.meas.shape[5] == 2          # CPE_MEAS_F32X2G: float2 (u, v) + gate byte (cpe_eval_host_uvg_f64)
+        self.compact = proto.meas.shape[5] == 2          # CPE_MEAS_F32X2G / B: float2 (u, v) + gate byte / bit (cpe_eval_host_uvg_f64)
+        self.bits = self.compact and proto.meas_gate.dim() == 2
+        self.gate_bytes = (self.N * self.C * 24 * self.W // (8 if self.bits else 1)) if self.compact else 0   # per sequence
         dev = model.device
         f64 = dict(dtype=torch.float64, device=dev)
         self.streams = [torch.cuda.Stream(device=dev) for _ in range(2)]
@@ -780,7 +797,7 @@ class HostEvaluator:
             st = dict(q=torch.empty(wave, self.N, 54, **f64),
                       meas=None if resident_meas else torch.empty(wave, self.N, self.C, 24, self.W, proto.meas.shape[5],
                                                                   dtype=proto.meas.dtype, device=dev),
-                      gate=torch.empty(wave, self.N, self.C, 24, self.W, dtype=torch.uint8, device=dev)
+                      gate=torch.empty(wave, self.gate_bytes, dtype=torch.uint8, device=dev)
                       if (self.compact and not resident_meas) else None,
                       frame_cost=torch.zeros(wave, self.N, 4, **f64), cost=torch.zeros(wave, 4, **f64),
                       jac=torch.empty(wave, self.N, self.C, model.jac_width, **f64) if jac else None,
@@ -791,21 +808,21 @@ class HostEvaluator:
         self.launches = 0
 
     def bytes_per_call(self):
-        mb = 0 if self.resident_meas else self.C * 24 * self.W * (
-            self.proto.meas.shape[5] * self.proto.meas.element_size() + (1 if self.compact else 0))
-        h2d = self.S * self.N * (54 * 8 + mb)
+        mb = 0 if self.resident_meas else self.C * 24 * self.W * self.proto.meas.shape[5] * self.proto.meas.element_size()
+        h2d = self.S * self.N * (54 * 8 + mb) + (0 if self.resident_meas else self.S * self.gate_bytes)
         d2h = self.S * 4 * 8 + (self.S * self.N * self.C * 24 * self.W * 2 * 8 if self.resid_out else 0)
         return h2d, d2h
 
     def __call__(self, h_q, h_meas=None, h_gate=None):
-        """h_q[S,N,54] f64 (and, unless resident_meas, h_meas[S,N,C,24,W,4|3|2] -- with h_gate[S,N,C,24,W] uint8 for the
-        compact layout) pinned host tensors -> pinned cost[S,4] (valid after return; `self.h_resid` holds the residuals
+        """h_q[S,N,54] f64 (and, unless resident_meas, h_meas[S,N,C,24,W,4|3|2] -- with h_gate[S,N,C,24,W] uint8, or its
+        bits [S, N*C*24*W/8], for the compact layouts) pinned host tensors -> pinned cost[S,4] (valid after return; `self.h_resid` holds the residuals
         with resid_out)."""
         assert not h_q.is_cuda and h_q.is_pinned()
         assert self.resident_meas == (h_meas is None)
         if h_meas is not None:
             assert not h_meas.is_cuda and h_meas.is_pinned()
             assert (h_gate is not None and h_gate.is_pinned() and h_gate.dtype == torch.uint8) == self.compact
+            assert not self.compact or h_gate[0].numel() == self.gate_bytes
         cur = torch.cuda.current_stream()
         for st in self.streams:
             st.wait_stream(cur)

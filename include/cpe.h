@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 117          /* 0.1.17 */
+#define CPE_VERSION 118          /* 0.1.17 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -66,6 +66,9 @@ extern "C" {
 #define CPE_MEAS_F32X2G 3        /* float2 {u, v} in cpe_batch.meas plus one byte per record in cpe_batch.meas_gate (0 / 1,
                                     the likelihood test done once on the host): 9 bytes per detection instead of 12 / 16 --
                                     the layout of choice when the detections cross PCIe (cpe_eval_host_uvg_f64) */
+#define CPE_MEAS_F32X2B 4        /* the same with the gates packed 8 per byte: bit (i & 7) of meas_gate[i >> 3] for the flat
+                                    record index i (numpy.packbits(..., bitorder="little")); 8.125 bytes per detection.  A
+                                    batch holds S * N * C * 24 * W records, always a multiple of 8 */
 
 #define CPE_LOSS_REDESCENDING 0  /* acinoset_misc.py:476-482, 2001-2015 */
 #define CPE_LOSS_SQUARE 1        /* hand-labelled data: (w slack)^2, camera multiplier not applied (acinoset_misc.py:471-474) */
@@ -165,7 +168,8 @@ typedef struct cpe_batch {
        the real cameras every sum keeps the order of the unpadded problem: results are bit-identical to a batch with
        C = n_cams[s].  The padded cams[] rows must still hold a valid camera.  NULL = C cameras for every sequence. */
     const int32_t *n_cams;          /* [S] optional */
-    const uint8_t *meas_gate;       /* [S,N,C,24,W] gates of CPE_MEAS_F32X2G (NULL for the other layouts) */
+    const uint8_t *meas_gate;       /* [S,N,C,24,W] gates of CPE_MEAS_F32X2G, or their bits for CPE_MEAS_F32X2B (NULL for the
+                                       other layouts) */
 } cpe_batch;
 
 /* Optional outputs of cpe_eval (NULL = skip). */
@@ -338,8 +342,9 @@ int cpe_grf_solve_f64(const cpe_batch *batch, const double *a, const double *Bm,
                       double *grf, double *resid, void *stream);
 
 /* The same for the compact layout CPE_MEAS_F32X2G: h_uv / d_uv hold float2 {u, v} records, h_gate / d_gate one byte each
- * (9 bytes per detection over PCIe instead of 12).  batch_dev->meas_layout must be CPE_MEAS_F32X2G; h_uv == NULL means the
- * detections are already resident in batch_dev->meas / meas_gate. */
+ * (9 bytes per detection over PCIe instead of 12), or one BIT each for CPE_MEAS_F32X2B (8.125 bytes).
+ * batch_dev->meas_layout must be one of the two; h_uv == NULL means the detections are already resident in
+ * batch_dev->meas / meas_gate. */
 int cpe_eval_host_uvg_f64(const cpe_model *model, const cpe_batch *batch_dev, const double *h_q, const void *h_uv,
                           const uint8_t *h_gate, double *d_q, void *d_uv, uint8_t *d_gate, const cpe_eval_out *out_dev,
                           double *d_cost, double *h_cost, double *h_resid, void *stream);

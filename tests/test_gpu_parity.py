@@ -350,15 +350,25 @@ def test_compact_layout_equals_dlc_native_and_pregated(gpu):
         b4 = engine.Batch.from_numpy(m4, prob.cams, prob.chain_vec, prob.h)
         assert np.array_equal(b2.meas_gate.cpu().numpy(), m4[..., 2].astype(np.uint8))
         assert int(b2.meas_gate[1, 2, 1, 5, 0]) == 0 and int(b2.meas_gate[2, 3, 4, 7, 0]) == 0
+        # gates packed 8 per byte (CPE_MEAS_F32X2B): numpy's little-endian packbits of the byte gates, from either layout
+        bb = b3.compact(bits=True)
+        assert bb.meas_layout == engine.MEAS_F32X2B and tuple(bb.meas_gate.shape) == (3, 8 * 6 * 24 * W // 8)
+        want_bits = np.packbits(b2.meas_gate.cpu().numpy().reshape(3, -1), axis=1, bitorder="little")
+        assert np.array_equal(bb.meas_gate.cpu().numpy(), want_bits)
+        assert torch.equal(b2.compact(bits=True).meas_gate, bb.meas_gate) and bb.compact(bits=True) is bb
+        sb = engine.Solver(gpu, bb)
+        ob = sb.evaluate(qd, resid=True, jac=True)
         s2, s3, s4 = (engine.Solver(gpu, b) for b in (b2, b3, b4))
         o2, o3, o4 = (s.evaluate(qd, resid=True, jac=True) for s in (s2, s3, s4))
+        for k in ("cost", "resid", "jac"):
+            assert torch.equal(ob[k], o3[k]), (W, k, "bit-packed vs DLC-native")
         for k in ("cost", "resid", "jac"):
             assert torch.equal(o2[k], o3[k]), (W, k, "compact vs DLC-native")
             assert torch.equal(o2[k], o4[k]), (W, k, "compact vs host-gated float4")
         assert bool(torch.isfinite(o2["cost"]).all())
         damp = torch.full((3,), 1e-2, dtype=torch.float64, device="cuda:0")
         d2, d3 = s2.lm_step(qd, damp)[0].clone(), s3.lm_step(qd, damp)[0].clone()
-        assert torch.equal(d2, d3), W
+        assert torch.equal(d2, d3) and torch.equal(sb.lm_step(qd, damp)[0], d3), W
         q0 = torch.as_tensor(prob.q_init, device="cuda:0")
         r2, r3 = s2.solve(q0, max_iter=8, n_outer=2), s3.solve(q0, max_iter=8, n_outer=2)
         for k in ("q", "cost", "counters", "status"):
@@ -619,16 +629,18 @@ def test_host_evaluator_modes_match_the_resident_evaluation(gpu):
         if resid_out:
             assert torch.equal(hev.h_resid, ref["resid"].cpu()) and d2h == 5 * 4 * 8 + ref["resid"].numel() * 8
     # the compact layout through its own entry point (cpe_eval_host_uvg_f64): float2 records + gate bytes cross the bus
-    cb = batch.compact()
-    h_uv, h_gate = cb.meas.cpu().pin_memory(), cb.meas_gate.cpu().pin_memory()
-    for resident, resid_out in ((False, False), (True, False), (False, True)):
-        hev = engine.HostEvaluator(gpu, cb, 5, 3, resident_meas=resident, resid_out=resid_out)
-        cost = hev(h_q, None if resident else h_uv, None if resident else h_gate)
-        assert torch.equal(cost, ref["cost"].cpu())
-        h2d, _ = hev.bytes_per_call()
-        assert h2d == 5 * 9 * 54 * 8 + (0 if resident else h_gate.numel() * 9)
-        if resid_out:
-            assert torch.equal(hev.h_resid, ref["resid"].cpu())
+    for bits in (False, True):
+        cb = batch.compact(bits=bits)
+        h_uv, h_gate = cb.meas.cpu().pin_memory(), cb.meas_gate.cpu().pin_memory()
+        n_det = 5 * 9 * 3 * 24
+        for resident, resid_out in ((False, False), (True, False), (False, True)):
+            hev = engine.HostEvaluator(gpu, cb, 5, 3, resident_meas=resident, resid_out=resid_out)
+            cost = hev(h_q, None if resident else h_uv, None if resident else h_gate)
+            assert torch.equal(cost, ref["cost"].cpu())
+            h2d, _ = hev.bytes_per_call()
+            assert h2d == 5 * 9 * 54 * 8 + (0 if resident else n_det * 8 + (n_det // 8 if bits else n_det))
+            if resid_out:
+                assert torch.equal(hev.h_resid, ref["resid"].cpu())
 
 
 def test_graph_replay_of_the_lm_iteration_is_bit_identical(gpu):
