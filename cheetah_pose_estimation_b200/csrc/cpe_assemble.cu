@@ -35,7 +35,7 @@ struct AsmParams {
     cpe_assemble_out ao;
     int TPF;        // C * 24
     int at_size;    // doubles of the aliased region (per-task blocks, then entries + group scratch)
-    int tab_doubles;    // shared-memory doubles taken by the table blob (k2_off[41] / 8, rounded up to 2)
+    int tab_doubles;    // shared-memory doubles taken by the table blob (k2_off[K2_OFF_END] / 8, rounded up to 2)
     int team_doubles;   // shared-memory doubles of one team: cam[C*24] + A_AT + at_size
     double ea, eb, ec, icb;     // exp(loss_a), exp(loss_b), exp(loss_c), 1 / (loss_c - loss_b)
 };
@@ -43,8 +43,13 @@ struct AsmParams {
 // per-frame shared layout (doubles), after cam[C*24]
 // sin/cos and the link rotations are dead once the per-frame items are done, i.e. before the first write to the aliased
 // region AT (per-pair blocks, then entries + elimination scratch): they live at its start.
-constexpr int A_QO = 0, A_POSO = 56, A_GV = 128, A_BV = 798, A_EQG = 1746, A_EQR = 1902, A_VIN = 1928, A_MOG = 1960,
-              A_DIAG = 2014, A_AT = 2068, A_SCO = A_AT, A_RO = A_AT + 104;
+// EQX = mu_eq * EQG sits right in front of EQR, and ACT (1 where an inequality row is violated) right in front of VIN, so
+// that the second factor of a joint / inequality item is ONE indexed load from a base chosen once per entry (Hessian
+// entry: EQX / ACT, gradient entry: EQR / VIN = the same index 156 / 32 doubles further)
+constexpr int A_QO = 0, A_POSO = 56, A_GV = 128, A_BV = 798, A_EQG = 1746, A_EQX = 1902, A_EQR = 2058, A_ACT = 2084,
+              A_VIN = 2116, A_MOG = 2148, A_DIAG = 2202, A_AT = 2256, A_SCO = A_AT, A_RO = A_AT + 104;
+static_assert(A_EQR - A_EQX == 156 && A_VIN - A_ACT == 32, "gradient entries read 156 / 32 doubles behind the Hessian ones");
+constexpr int K2_OFF_BLK = 41, K2_OFF_END = 45, K2_BLK_SLOTS = 8;      // must match skeleton.py
 constexpr int G_U0 = 10, B_U0 = 216, B_G0 = 876, GRAD_Q = 63;       // must match skeleton.py
 constexpr int ENT_PAD = 640, DDI_SZ = CPE_MAX_GROUPS * 72, YS_SZ = CPE_MAX_GROUPS * 78;
 
@@ -70,7 +75,7 @@ __global__ void __launch_bounds__(TEAM_T *NTEAM, 1) assemble_kernel(const __grid
     {
         const uint4 *src = reinterpret_cast<const uint4 *>(p.m.k2_tab);
         uint4 *dst = reinterpret_cast<uint4 *>(sm);
-        for (int i = threadIdx.x; i < p.m.k2_off[41] / 16; i += TEAM_T * NTEAM) dst[i] = src[i];
+        for (int i = threadIdx.x; i < p.m.k2_off[K2_OFF_END] / 16; i += TEAM_T * NTEAM) dst[i] = src[i];
     }
     __syncthreads();
     const unsigned char *tab = reinterpret_cast<const unsigned char *>(sm);
@@ -79,6 +84,10 @@ __global__ void __launch_bounds__(TEAM_T *NTEAM, 1) assemble_kernel(const __grid
     const int16_t *t_grp = reinterpret_cast<const int16_t *>(tab + p.m.k2_off[2]);
     const int team = threadIdx.x / TEAM_T, tid = threadIdx.x - team * TEAM_T;
     constexpr int nt = TEAM_T;
+    const int lane = tid & 31, wid = tid >> 5;
+    // blocks of 32 gather work items this warp owns (balanced on the host: skeleton._balanced_blocks)
+    const unsigned char *h_blk = tab + p.m.k2_off[K2_OFF_BLK + (TEAM_T == 160 ? 0 : 2)] + wid * K2_BLK_SLOTS;
+    const unsigned char *s_blk = tab + p.m.k2_off[K2_OFF_BLK + (TEAM_T == 160 ? 1 : 3)] + wid * K2_BLK_SLOTS;
     const int N = p.b.N, C = p.b.C, W = p.b.W, TPF = p.TPF;
     const int n_ineq = p.m.n_ineq, n_u = p.m.n_u, n_ent = p.m.n_ent;
     double *cam = sm + p.tab_doubles + (size_t)team * p.team_doubles;
@@ -89,6 +98,11 @@ __global__ void __launch_bounds__(TEAM_T *NTEAM, 1) assemble_kernel(const __grid
     const int mc = tid / 24, ml = tid - mc * 24;
     const long long total = (long long)p.b.S * N, stride = (long long)gridDim.x * NTEAM;
     long long f = (long long)blockIdx.x * NTEAM + team;
+    // (sequence, frame) of f, advanced with the stride in 32-bit arithmetic (S * N < 2^31 is checked by the host)
+    const int st_s = (int)(stride / N), st_k = (int)(stride - (long long)st_s * N);
+    int s = (int)(f / N), k = (int)(f - (long long)s * N);
+    s -= st_s; k -= st_k;
+    if (k < 0) { k += N; --s; }
     // registers of the frame in flight: one coordinate and one detection per thread, fetched one frame ahead
     double q_pre = 0.0;
     MeasRaw m_pre;
@@ -99,7 +113,8 @@ __global__ void __launch_bounds__(TEAM_T *NTEAM, 1) assemble_kernel(const __grid
     }
     int s_cam = -1;                                      // sequence whose cameras sit in `cam`
     for (; f < total; f += stride) {
-    const int s = (int)(f / N), k = (int)(f - (long long)s * N);
+    s += st_s; k += st_k;
+    if (k >= N) { k -= N; ++s; }
     const int nf = p.b.n_frames[s];
     const double q_cur = q_pre;
     MeasRaw mraw = m_pre;
@@ -180,9 +195,11 @@ __global__ void __launch_bounds__(TEAM_T *NTEAM, 1) assemble_kernel(const __grid
                 for (int x = 0; x < 3; ++x) {
                     double d[3];
                     drot_times(fr + A_SCO + 6 * la, x, ea0, ea1, ea2, d);
-                    fr[A_EQG + e * 6 + x] = d[0] * b0 + d[1] * b1 + d[2] * b2;
+                    const double ga = d[0] * b0 + d[1] * b1 + d[2] * b2;
                     drot_times(fr + A_SCO + 6 * lb, x, eb0, eb1, eb2, d);
-                    fr[A_EQG + e * 6 + 3 + x] = a0 * d[0] + a1 * d[1] + a2 * d[2];
+                    const double gb = a0 * d[0] + a1 * d[1] + a2 * d[2];
+                    fr[A_EQG + e * 6 + x] = ga; fr[A_EQX + e * 6 + x] = mu_eq * ga;
+                    fr[A_EQG + e * 6 + 3 + x] = gb; fr[A_EQX + e * 6 + 3 + x] = mu_eq * gb;
                 }
                 continue;
             }
@@ -194,7 +211,9 @@ __global__ void __launch_bounds__(TEAM_T *NTEAM, 1) assemble_kernel(const __grid
                 const double d = fr[A_QO + ip] - (im >= 0 ? fr[A_QO + im] : 0.0);
                 const double lam = p.b.lam_in ? p.b.lam_in[fidx * n_ineq + j] : 0.0;
                 const double t = d + lam / mu_in;
-                fr[A_VIN + j] = t - fmin(fmax(t, lo), up);
+                const double v = t - fmin(fmax(t, lo), up);
+                fr[A_VIN + j] = v;
+                fr[A_ACT + j] = v != 0.0 ? 1.0 : 0.0;
                 continue;
             }
             it -= n_ineq;
@@ -309,7 +328,11 @@ __global__ void __launch_bounds__(TEAM_T *NTEAM, 1) assemble_kernel(const __grid
     // slot-major tables in shared memory (skeleton.k2_tables): lane <-> consecutive eo, no bank conflicts, no address
     // that depends on a loaded index
     {
-        for (int eo = tid; eo < n_ent; eo += nt) {
+        for (int bi = 0; bi < K2_BLK_SLOTS; ++bi) {
+            const int blk = h_blk[bi];
+            if (blk == 255) break;
+            const int eo = blk * 32 + lane;
+            if (eo >= n_ent) continue;
             const uint2 m = t_meta[eo];
             const int e = m.x & 1023, pp = (m.x >> 10) & 63, qq = (m.x >> 16) & 63;
             const int na = m.y & 255, ne = (m.y >> 8) & 255, ni = m.y >> 16;
@@ -322,16 +345,16 @@ __global__ void __launch_bounds__(TEAM_T *NTEAM, 1) assemble_kernel(const __grid
                 acc += g[0] * b[0] + g[1] * b[1] + g[2] * b[2];
             }
             double acce = 0.0;
+            const double *ex = fr + (grad ? A_EQR : A_EQX);        // second factor: mu_eq * eqg[j], or the row's residual
             for (int i = 0; i < ne; ++i) {
                 const int it = reinterpret_cast<const uint16_t *>(tab + p.m.k2_off[27 + i])[eo];
-                const double gi = fr[A_EQG + (it >> 8)];
-                acce += gi * (grad ? fr[A_EQR + (it & 255)] : mu_eq * fr[A_EQG + (it & 255)]);
+                acce += fr[A_EQG + (it >> 8)] * ex[it & 255];
             }
             double acci = 0.0;
+            const double *vx = fr + (grad ? A_VIN : A_ACT);
             for (int i = 0; i < ni; ++i) {
                 const int it = (tab + p.m.k2_off[32 + i])[eo];
-                const double v = fr[A_VIN + (it >> 1)];
-                const double val = grad ? v : (v != 0.0 ? 1.0 : 0.0);
+                const double val = vx[it >> 1];
                 acci += (it & 1) ? -val : val;
             }
             acc += acce + mu_in * acci;
@@ -359,7 +382,7 @@ __global__ void __launch_bounds__(TEAM_T *NTEAM, 1) assemble_kernel(const __grid
     // ---- per-frame elimination of the dependent coordinates: one warp per group, tableau column per lane ----------
     const double damp = p.damp[s];
     constexpr int GD = CPE_GRP_MAX_DEP, GN = CPE_GRP_MAX_NB, TW = GD + GN + 1;
-    const int lane = tid & 31, wid = tid >> 5, nw = nt >> 5;
+    constexpr int nw = nt >> 5;
     const int n_groups = p.m.n_groups;
     for (int g = wid; g < n_groups; g += nw) {
         double t[GD];
@@ -401,8 +424,12 @@ __global__ void __launch_bounds__(TEAM_T *NTEAM, 1) assemble_kernel(const __grid
     team_sync<TEAM_T>(team);
     // ---- reduced block S = H_ii + damping - sum_g Hdi^T Y and ghat = g_i - sum_g Hdi^T y (static gather) ----------------
     double *So = p.ao.S + fidx * 784;
-    const int n_swork = p.m.k2_off[42];               // lower triangle of S + the reduced gradient
-    for (int eo = tid; eo < n_swork; eo += nt) {
+    const int n_swork = p.m.k2_off[K2_OFF_END + 1];   // lower triangle of S + the reduced gradient
+    for (int bi = 0; bi < K2_BLK_SLOTS; ++bi) {
+        const int blk = s_blk[bi];
+        if (blk == 255) break;
+        const int eo = blk * 32 + lane;
+        if (eo >= n_swork) continue;
         const uint32_t m = t_smeta[eo];
         const int r = m & 31, c = (m >> 5) & 31, ns = (m >> 10) & 7, si = m >> 13;
         double v = si != 1023 ? ENT[si] : 0.0;
@@ -464,8 +491,8 @@ extern "C" int cpe_assemble_f64(const cpe_model *model, const cpe_batch *b, cons
     const int need = ENT_PAD + DDI_SZ + YS_SZ;
     p.at_size = p.TPF * 9 > need ? p.TPF * 9 : need;
     p.team_doubles = (b->C * CPE_CAM_STRIDE + A_AT + p.at_size + 1) & ~1;
-    p.tab_doubles = ((model->k2_off[41] + 15) / 16) * 2;
-    if (model->k2_off[41] <= 0 || model->k2_off[41] % 16) return CPE_E_DIM;
+    p.tab_doubles = ((model->k2_off[K2_OFF_END] + 15) / 16) * 2;
+    if (model->k2_off[K2_OFF_END] <= 0 || model->k2_off[K2_OFF_END] % 16) return CPE_E_DIM;
     if (p.TPF <= 160) {
         // five teams: 25 warps at 72 registers.  Measured at 1776 x 500 (profiles/r2i_k2_teams.txt): 6 teams / 64 registers
         // 31.2 ms, 5 / 72: 29.3 ms, 4 / 96: 30.0 ms, 3 / 128: 32.9 ms

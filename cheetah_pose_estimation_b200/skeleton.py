@@ -478,7 +478,26 @@ def assemble_tables(t=None, kinetic_dataset=False):
 K2_ENT_PAD = 640            # >= n_ent, multiple of 32 (include/cpe.h CPE_K2_ENT_PAD)
 K2_S_PAD = 832              # >= 28 * 29
 K2_MAX_A, K2_MAX_E, K2_MAX_I, K2_MAX_S = 24, 5, 4, 5
-K2_OFF_META, K2_OFF_SMETA, K2_OFF_GRP, K2_OFF_A, K2_OFF_E, K2_OFF_I, K2_OFF_S, K2_OFF_END = 0, 1, 2, 3, 27, 32, 36, 41
+K2_OFF_META, K2_OFF_SMETA, K2_OFF_GRP, K2_OFF_A, K2_OFF_E, K2_OFF_I, K2_OFF_S, K2_OFF_BLK, K2_OFF_END = 0, 1, 2, 3, 27, 32, 36, 41, 45
+K2_BLK_SLOTS = 8            # blocks of 32 work items one warp can be given (255 = none)
+
+
+def _balanced_blocks(costs, n_warps):
+    """Blocks of 32 consecutive work items dealt to the warps of a team, longest processing time first, so that every
+    warp of the team reaches the barrier behind the gather at about the same time (a round-robin deal gives warp 0 the
+    heaviest block of every round: 1.6x the mean).  Returns uint8[n_warps, K2_BLK_SLOTS], 255-padded; a warp walks its
+    row in ascending block order."""
+    load = np.zeros(n_warps)
+    rows = [[] for _ in range(n_warps)]
+    for b in sorted(range(len(costs)), key=lambda b: (-costs[b], b)):
+        w = int(np.argmin(load))
+        load[w] += costs[b]
+        rows[w].append(b)
+    out = np.full((n_warps, K2_BLK_SLOTS), 255, np.uint8)
+    for w, r in enumerate(rows):
+        assert len(r) <= K2_BLK_SLOTS
+        out[w, :len(r)] = sorted(r)
+    return out
 
 
 def k2_tables(a, ind_idx):
@@ -494,7 +513,9 @@ def k2_tables(a, ind_idx):
         a slots    int32  (offset in G space << 16) | offset in B space
         e slots    uint16 (eqg index << 8) | (eqg index | eq row)        i slots  uint8  (row << 1) | negative
         smeta[eo]  uint32 r | c << 5 | n_s << 10 | src << 13   (src = entry of H(ind_r, ind_c) or g(ind_r); 1023 = none)
-        s slots    uint16 (group << 8) | (a << 4) | b                     grp      int16  tableau sources"""
+        s slots    uint16 (group << 8) | (a << 4) | b                     grp      int16  tableau sources
+        blk        uint8  [K2_OFF_BLK + 0 / 1] = blocks of 32 entries / Schur items per warp of a 5-warp team (160 threads),
+                          [+ 2 / 3] the same for a 6-warp team (192 threads): _balanced_blocks"""
     n_ent = int(a["n_ent"])
     assert n_ent <= K2_ENT_PAD and n_ent < 1024
 
@@ -538,6 +559,15 @@ def k2_tables(a, ind_idx):
     sections += [x.view(np.uint8) for x in slots(le, K2_MAX_E, np.uint16, K2_ENT_PAD)]
     sections += [x.view(np.uint8) for x in slots(li, K2_MAX_I, np.uint8, K2_ENT_PAD)]
     sections += [x.view(np.uint8) for x in slots(ls_, K2_MAX_S, np.uint16, K2_S_PAD)]
+    # per-block cost in warp-instructions (profiles/r2r_ncu_k2_phases.txt): a block runs as long as its longest lists
+    def blocks(ls_of_kind, weights, fixed):
+        n = len(ls_of_kind[0])
+        return [fixed + sum(wt * max(len(l) for l in kind[b0:b0 + 32]) for kind, wt in zip(ls_of_kind, weights))
+                for b0 in range(0, n, 32)]
+    h_cost = blocks((la, le, li), (25, 12, 10), 60)
+    s_cost = blocks((ls_,), (30,), 40)
+    for nw in (5, 6):
+        sections += [_balanced_blocks(h_cost, nw).reshape(-1), _balanced_blocks(s_cost, nw).reshape(-1)]
     assert len(sections) == K2_OFF_END
     off, blob = [], []
     pos = 0

@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 118          /* 0.1.17 */
+#define CPE_VERSION 119          /* 0.1.17 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -128,7 +128,9 @@ typedef struct cpe_model {
        tables above remain the definition (tests/test_assemble_tables.py checks the blob against them).
        k2_off[] = byte offsets of the sections: [0] meta uint2[CPE_K2_ENT_PAD], [1] smeta uint32[CPE_K2_S_PAD],
        [2] grp int16, [3..26] a slots int32, [27..31] e slots uint16, [32..35] i slots uint8, [36..40] s slots uint16,
-       [41] total bytes (multiple of 16), [42] number of Schur work items (lower triangle of S + reduced gradient). */
+       [41..44] uint8 block lists: which blocks of 32 entries / Schur items each warp of a team gathers (41 and 42 for
+       5-warp teams, 43 and 44 for 6-warp teams, 8 slots per warp, 255 = none), [45] total bytes (multiple of 16),
+       [46] number of Schur work items (lower triangle of S + reduced gradient). */
     const void *k2_tab;
     int32_t k2_off[48];
 } cpe_model;

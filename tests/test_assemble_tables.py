@@ -168,3 +168,12 @@ def test_k2_table_blob_holds_the_same_lists_in_processing_order():
         assert (m >> 13) == (src if src >= 0 else 1023)
     grp = sec(sk.K2_OFF_GRP, np.int16)
     assert np.array_equal(grp[:len(at["grp_src"])], at["grp_src"])
+    # block lists: every block of 32 work items belongs to exactly one warp of the team, ascending within a warp, and no
+    # warp carries more than 1.25 x the mean modelled load (a round-robin deal reaches 1.6 x)
+    for k, (n_warps, n_items) in enumerate(((5, at["n_ent"]), (5, len(work)), (6, at["n_ent"]), (6, len(work)))):
+        rows = sec(sk.K2_OFF_BLK + k, np.uint8)[:n_warps * sk.K2_BLK_SLOTS].reshape(n_warps, sk.K2_BLK_SLOTS)
+        used = [int(b) for r in rows for b in r if b != 255]
+        assert sorted(used) == list(range((int(n_items) + 31) // 32))
+        for r in rows:
+            own = [int(b) for b in r if b != 255]
+            assert own == sorted(own) and all(b == 255 for b in r[len(own):])
