@@ -313,3 +313,60 @@ def determine_contacts_from_states(fte_states, animal, start_frame, fps, ground_
     pos, vel = foot_height_and_velocity(fte_states["q"], fte_states["dq"], lengths, radii)
     speed = float(np.mean(np.linalg.norm(np.asarray(fte_states["com_vel"]), axis=1)))
     return contact_detection(pos[:, :, 2], vel[:, :, 2], start_frame, speed, fps, ground_plane_height, data_dir)
+
+
+# ---- contact prescription (acinoset_opt.py:783-812, acinoset_misc.py:1140-1167) as bound arrays ---------------------------
+def contact_times(contact_json, n_frames=None):
+    """Per foot (FEET order) the sorted 1-based frame indices `fe` at which it is prescribed to be on the ground, from an
+    `autogen-contact.json` / metadata dict: every [first, last] range INCLUSIVE of both ends, shifted by the file's
+    start_frame, plus one for the Pyomo indexing (acinoset_opt.py:795-803; `estimate_grf` reads the same ranges half-open,
+    see contact_mask).  Feet whose entry is null get an empty list.  `n_frames` clips to the trajectory."""
+    start = int(contact_json["start_frame"])
+    out = []
+    for name in FEET:
+        times = []
+        for seq in (contact_json["contacts"].get(name) or []):
+            times += list(range(int(seq[0]) - start + 1, int(seq[1]) - start + 2))
+        if n_frames is not None:
+            times = [t for t in times if 1 <= t <= n_frames]
+        out.append(times)
+    return out
+
+
+def prescribe_contact_order(ground_timings, n_frames, foot_height_uncertainty=0.05, min_GRFz=0.01):
+    """misc.prescribe_contact_order (acinoset_misc.py:1140-1167) without the Pyomo model: what it fixes and bounds, as
+    arrays [n_frames, 4] in FEET order (row fe - 1 for the 1-based index fe of `ground_timings`, one list per foot):
+      stance           bool: the foot is prescribed on the ground
+      grfz_lb/grfz_ub  flight: both 0 (GRFz and GRFxy are fixed to 0); stance: [min_GRFz, inf)
+      grfxy_ub         flight: 0; stance: inf
+      height_lb/ub     stance: -/+ foot_height_uncertainty (None: unbounded), flight: unbounded
+    `contact_violations` evaluates a trajectory against them."""
+    stance = np.zeros((n_frames, 4), dtype=bool)
+    for f, times in enumerate(ground_timings):
+        for fe in times:
+            assert 1 <= fe <= n_frames, (fe, n_frames)
+            stance[fe - 1, f] = True
+    inf = np.inf
+    hu = inf if foot_height_uncertainty is None else float(foot_height_uncertainty)
+    return dict(stance=stance, grfz_lb=np.where(stance, float(min_GRFz), 0.0), grfz_ub=np.where(stance, inf, 0.0),
+                grfxy_ub=np.where(stance, inf, 0.0), height_lb=np.where(stance, -hu, -inf), height_ub=np.where(stance, hu, inf))
+
+
+def contact_violations(q, dq, lengths, radii, bounds, grf=None, ground_plane_height=0.0):
+    """How far a trajectory is from a contact prescription: per foot the largest distance of the foot height (above the
+    ground plane) outside [height_lb, height_ub] over the prescribed stance frames, the largest horizontal foot speed
+    there (the reference's no-slip rows, acinoset_opt.py:805-806), and -- with grf[N,20] (`pack_grf` layout) -- the
+    largest force applied in flight and the largest shortfall below min_GRFz in stance."""
+    pos, vel = foot_height_and_velocity(q, dq, lengths, radii)
+    n = bounds["stance"].shape[0]
+    hgt = pos[:n, :, 2] - ground_plane_height
+    st = bounds["stance"]
+    out_h = np.maximum(np.maximum(bounds["height_lb"] - hgt, hgt - bounds["height_ub"]), 0.0)
+    slip = np.where(st, np.linalg.norm(vel[:n, :, 0:2], axis=-1), 0.0)
+    res = dict(height=out_h.max(axis=0), slip_speed=slip.max(axis=0))
+    if grf is not None:
+        g = np.asarray(grf, np.float64)[:n]
+        fz, fxy = g[:, 0:4], g[:, 4:20].reshape(n, 4, 4)
+        res["flight_force"] = np.where(st, 0.0, np.abs(fz) + np.abs(fxy).sum(-1)).max(axis=0)
+        res["stance_shortfall"] = np.where(st, np.maximum(bounds["grfz_lb"] - fz, 0.0), 0.0).max(axis=0)
+    return res

@@ -303,3 +303,42 @@ def test_foot_velocity_is_the_time_derivative_of_the_foot_position(golden_dir):
     pose = kinematics.fk(q, cl, cv)
     for f, name in enumerate(kinetics.FEET):
         assert np.abs(pose[:, sk.MARKERS.index(kinetics.PAW_MARKERS[name])] - pos[:, f]).max() < 1e-13
+
+
+def test_contact_prescription_as_bound_arrays(golden_dir):
+    """kinetics.contact_times / prescribe_contact_order (acinoset_opt.py:795-812, acinoset_misc.py:1140-1167) on a shipped
+    contact file: 1-based INCLUSIVE stance indices, GRF fixed to zero in flight, GRFz >= 0.01 and the foot height within
+    the uncertainty band in stance; the shipped trajectory itself keeps its feet within 0.1 m of the ground plane in the
+    stance frames the shipped file prescribes (the reference's band for AcinoSet clips, acinoset_opt.py:782)."""
+    import json
+    from cheetah_pose_estimation_b200 import kinetics
+    g = np.load(os.path.join(golden_dir, "contacts_ref.npz"))
+    q, dq = g["0_q"], g["0_dq"]
+    n = q.shape[0]
+    start = int(g["0_start_frame"])
+    cj = {"start_frame": start, "end_frame": start + n, "contacts": json.loads(str(g["0_contacts"]))}
+    times = kinetics.contact_times(cj, n_frames=n)
+    assert len(times) == 4 and any(times)
+    for f, name in enumerate(kinetics.FEET):
+        want = []
+        for seq in (cj["contacts"].get(name) or []):
+            want += [fe for fe in range(seq[0] - start + 1, seq[1] - start + 2) if 1 <= fe <= n]      # inclusive, 1-based
+        assert times[f] == want
+    b = kinetics.prescribe_contact_order(times, n, foot_height_uncertainty=0.1)
+    st = b["stance"]
+    assert st.shape == (n, 4) and [int(x) for x in st.sum(0)] == [len(set(t)) for t in times]
+    assert np.all(b["grfz_ub"][~st] == 0.0) and np.all(b["grfxy_ub"][~st] == 0.0) and np.all(b["grfz_lb"][~st] == 0.0)
+    assert np.all(b["grfz_lb"][st] == 0.01) and np.all(np.isinf(b["grfz_ub"][st]))
+    assert np.all(b["height_ub"][st] == 0.1) and np.all(b["height_lb"][st] == -0.1) and np.all(np.isinf(b["height_ub"][~st]))
+    # the half-open mask estimate_grf uses covers the same ranges minus their last frame
+    mask = kinetics.contact_mask(cj).astype(bool)
+    assert np.all(st[:-1][mask[:-1]]) and st.sum() >= mask.sum()
+    lengths, radii, _ = sk.animal(str(g["0_animal"]))
+    grf = np.zeros((n, 20))
+    grf[:, 0:4] = np.where(st, 0.5, 0.0)
+    grf[0, 0] = 0.25 if not st[0, 0] else 0.0                           # a force in flight (if the foot is in flight there)
+    v = kinetics.contact_violations(q, dq, lengths, radii, b, grf=grf, ground_plane_height=float(g["0_ground"]))
+    assert v["height"].shape == (4,) and v["height"].max() < 0.05, v
+    assert v["stance_shortfall"].max() == 0.0 and v["flight_force"][0] == (0.25 if not st[0, 0] else 0.0)
+    unbounded = kinetics.prescribe_contact_order(times, n, foot_height_uncertainty=None)
+    assert np.all(np.isinf(unbounded["height_ub"]))
