@@ -100,6 +100,8 @@ EXPORTS = {
     "cpe_eom_slack_noalloc_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p, c_f64p, C.c_void_p]),
     "cpe_torque_costs_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, C.c_int32, c_f64p, c_f64p, c_f64p, c_f64p, c_f64p,
                                        C.c_void_p]),
+    "cpe_eom_vjp_f64": (C.c_int, [C.POINTER(CpeBatch), c_f64p, c_f64p, c_f64p, c_f64p, c_f64p, c_f64p, c_f64p, c_f64p, c_f64p,
+                                  c_f64p, C.c_void_p]),
     "cpe_eval_host_uvg_f64": (C.c_int, [C.POINTER(CpeModel), C.POINTER(CpeBatch), C.c_void_p, C.c_void_p, C.c_void_p, c_f64p,
                                         C.c_void_p, C.c_void_p, C.POINTER(CpeEvalOut), c_f64p, C.c_void_p, C.c_void_p,
                                         C.c_void_p]),

@@ -49,6 +49,67 @@ def eom_rows(q, dq, ddq, grf, par, n_frames=None, device="cuda"):
     return out
 
 
+def eom_vjp(q, dq, ddq, grf, par, w=None, n_frames=None, device="cuda"):
+    """Vector-Jacobian product of the EOM rows with respect to the states (`cpe_eom_vjp_f64`): returns
+    (eom[S,N,6], g_q, g_dq, g_ddq [S,N,54]) with g = sum_i w[..., i] d row_i / d (q, dq, ddq).  w = None takes
+    w = 2 * rows: the gradient of misc.eom_slack_cost (acinoset_misc.py:631-636) -- in the reference's kinetic NLP q, dq
+    and ddq are separate variables tied by the collocation constraints, so these three partials are what ASL evaluates
+    for that term (acinoset_opt.py:905-921).  `states_gradient_to_q` folds them onto q alone."""
+    if not torch.cuda.is_available():
+        raise _lib.CpeError("CUDA device required: the hot path has no CPU fallback")
+    lib = _lib.load()
+    dev = torch.device(device)
+    t = [_t(a, dev) for a in (q, dq, ddq, grf, par)]
+    S, N = t[0].shape[:2]
+    assert all(x.shape == (S, N, 54) for x in t[:3]) and t[3].shape == (S, N, N_FORCES) and t[4].shape == (S, N_PAR)
+    wt = None if w is None else _t(w, dev)
+    assert wt is None or wt.shape == (S, N, 6)
+    b, keep = _dev_batch(S, N, 1.0, n_frames, dev)
+    f64 = dict(dtype=torch.float64, device=dev)
+    eom = torch.zeros(S, N, 6, **f64)
+    g = [torch.zeros(S, N, 54, **f64) for _ in range(3)]
+    p = lambda x: None if x is None else C.c_void_p(x.data_ptr())
+    _lib.check(lib.cpe_eom_vjp_f64(C.byref(b), *[p(x) for x in t], p(wt), p(eom), p(g[0]), p(g[1]), p(g[2]),
+                                   C.c_void_p(torch.cuda.current_stream().cuda_stream)), "cpe_eom_vjp_f64")
+    return eom, g[0], g[1], g[2]
+
+
+def rates_from_q(q, h):
+    """dq, ddq of the mirrored API from q[..., N, 54] (acinoset_opt._finish_estimate: implicit Euler, collocation.py:58-68,
+    free boundary values ddq_0 = ddq_1 = ddq_2 and dq_0 = dq_1 - h ddq_1).  torch, any device."""
+    dq = torch.zeros_like(q)
+    ddq = torch.zeros_like(q)
+    dq[..., 1:, :] = (q[..., 1:, :] - q[..., :-1, :]) / h
+    ddq[..., 2:, :] = (dq[..., 2:, :] - dq[..., 1:-1, :]) / h
+    if q.shape[-2] > 2:
+        ddq[..., 1, :] = ddq[..., 2, :]
+        ddq[..., 0, :] = ddq[..., 2, :]
+        dq[..., 0, :] = dq[..., 1, :] - h * ddq[..., 1, :]
+    return dq, ddq
+
+
+def states_gradient_to_q(g_q, g_dq, g_ddq, h):
+    """Adjoint of `rates_from_q`: d cost / d q [..., N, 54] of a cost whose partials with respect to q, dq, ddq are given
+    and whose dq, ddq are the mirrored API's functions of q.  N > 2."""
+    N = g_q.shape[-2]
+    assert N > 2
+    g_dq, g_ddq = g_dq.clone(), g_ddq.clone()
+    out = g_q.clone()
+    # dq_0 = dq_1 - h ddq_1 ; ddq_0 = ddq_1 = ddq_2
+    g_dq[..., 1, :] += g_dq[..., 0, :]
+    g_ddq[..., 1, :] -= h * g_dq[..., 0, :]
+    g_dq[..., 0, :] = 0.0
+    g_ddq[..., 2, :] += g_ddq[..., 0, :] + g_ddq[..., 1, :]
+    g_ddq[..., 0:2, :] = 0.0
+    # ddq_n = (dq_n - dq_{n-1}) / h, n >= 2
+    g_dq[..., 2:, :] += g_ddq[..., 2:, :] / h
+    g_dq[..., 1:-1, :] -= g_ddq[..., 2:, :] / h
+    # dq_n = (q_n - q_{n-1}) / h, n >= 1
+    out[..., 1:, :] += g_dq[..., 1:, :] / h
+    out[..., :-1, :] -= g_dq[..., 1:, :] / h
+    return out
+
+
 def estimate_grf(q, dq, ddq, par, contact, n_frames=None, iters=600, device="cuda"):
     """Per-frame GRF estimate of CheetahEstimator.estimate_grf (acinoset_opt.py:176-249) for S sequences at once.
 

@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 119          /* 0.1.17 */
+#define CPE_VERSION 120          /* 0.1.17 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -366,6 +366,14 @@ int cpe_eom_slack_f64(const cpe_batch *batch, const double *eom, const double *B
                       double *grad_f, void *stream);
 int cpe_torque_costs_f64(const cpe_batch *batch, const double *Tc, int32_t n_axes, const double *weight, double *frame_work,
                          double *cost, double *grad_sq, double *grad_ch, void *stream);
+
+/* Vector-Jacobian product of rows 0-5 of the equations of motion (cpe_eom_f64, same inputs) with respect to the states:
+ *   g_q, g_dq, g_ddq [S,N,54] = sum_i w[s,n,i] * d row_i / d (q, dq, ddq)      (frames beyond n_frames[s]: zeros)
+ * w[S,N,6] == NULL takes w = 2 * rows: the gradient of the EOM slack cost sum_i row_i^2 (misc.eom_slack_cost,
+ * acinoset_misc.py:631-636) -- the derivative ASL hands IPOPT for that term of the kinetic objective (acinoset_opt.py:905-921).
+ * eom[S,N,6] (may be NULL) receives the rows.  Adjoint sweep of the generated program (oracle/derive_eom_grad.py). */
+int cpe_eom_vjp_f64(const cpe_batch *batch, const double *q, const double *dq, const double *ddq, const double *grf,
+                    const double *par, const double *w, double *eom, double *g_q, double *g_dq, double *g_ddq, void *stream);
 
 /* Allocation-free variant of cpe_eom_slack_f64.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that

@@ -188,3 +188,69 @@ def test_grf_of_a_real_shipped_trajectory(golden_dir):
             assert not F.any()
     # stance forces point up: vertical force of every foot in contact is positive somewhere in its stance
     assert all(max(gz[f]) > 0.0 for f in kinetics.FEET)
+
+
+def test_rates_adjoint_matches_autograd():
+    """kinetics.states_gradient_to_q is the adjoint of kinetics.rates_from_q (the mirrored API's dq / ddq from q, incl. the
+    free boundary values): checked against torch.autograd on the CPU."""
+    import torch
+    from cheetah_pose_estimation_b200 import kinetics
+    g = torch.Generator().manual_seed(3)
+    q = torch.randn(2, 9, 54, dtype=torch.float64, generator=g, requires_grad=True)
+    a, b, c = (torch.randn(2, 9, 54, dtype=torch.float64, generator=g) for _ in range(3))
+    h = 1.0 / 120.0
+    dq, ddq = kinetics.rates_from_q(q, h)
+    ((a * q).sum() + (b * dq).sum() + (c * ddq).sum()).backward()
+    got = kinetics.states_gradient_to_q(a, b, c, h)
+    assert torch.allclose(got, q.grad, rtol=1e-12, atol=1e-9 * float(q.grad.abs().max()))
+
+
+@pytest.mark.gpu
+def test_eom_vjp_matches_complex_step_jacobian(golden_dir):
+    """cpe_eom_vjp_f64 (adjoint sweep of the generated EOM program) against d rows / d (q, dq, ddq) obtained by complex-step
+    differentiation of sympy.lambdify of the reference-derived expressions (tests/golden/eom_grad_ref.npz,
+    oracle/derive_eom_grad.py): random weights, the slack-cost default w = 2 rows, rows returned alongside, ragged batch."""
+    import torch
+    from cheetah_pose_estimation_b200 import kinetics
+    g = np.load(os.path.join(golden_dir, "eom_grad_ref.npz"))
+    n = g["q"].shape[0]
+    jac = g["jac"]                                                   # [n, 6, 162]
+    rng = np.random.default_rng(5)
+    w = rng.normal(size=(n, 6))
+    sh = lambda x: x[:, None]                                        # n sequences of one frame: par differs per sample
+    eom, gq, gdq, gddq = kinetics.eom_vjp(sh(g["q"]), sh(g["dq"]), sh(g["ddq"]), sh(g["F"]), g["par"], w=sh(w))
+    got = torch.cat([gq, gdq, gddq], dim=-1)[:, 0].cpu().numpy()
+    want = np.einsum("ni,nij->nj", w, jac)
+    scale = np.abs(want).max(axis=1, keepdims=True)
+    assert np.abs(got - want).max() / scale.max() < 1e-10 and (np.abs(got - want) / scale).max() < 1e-9
+    assert np.abs(eom[:, 0].cpu().numpy() - g["eom"]).max() < 1e-9 * np.abs(g["eom"]).max()
+    # default weights: gradient of sum_i row_i^2
+    _, gq, gdq, gddq = kinetics.eom_vjp(sh(g["q"]), sh(g["dq"]), sh(g["ddq"]), sh(g["F"]), g["par"])
+    got = torch.cat([gq, gdq, gddq], dim=-1)[:, 0].cpu().numpy()
+    want = 2.0 * np.einsum("ni,nij->nj", g["eom"], jac)
+    assert (np.abs(got - want) / np.abs(want).max(axis=1, keepdims=True)).max() < 1e-9
+    # one sequence of n frames, the last two beyond n_frames: zeros there, the others unchanged
+    par0 = np.tile(g["par"][0], (n, 1))
+    one = lambda x: x[None]
+    e1, a1, b1, c1 = kinetics.eom_vjp(one(g["q"]), one(g["dq"]), one(g["ddq"]), one(g["F"]), par0[:1], n_frames=[n - 2])
+    e2, a2, b2, c2 = kinetics.eom_vjp(one(g["q"]), one(g["dq"]), one(g["ddq"]), one(g["F"]), par0[:1])
+    for x1, x2 in ((e1, e2), (a1, a2), (b1, b2), (c1, c2)):
+        assert torch.equal(x1[0, :n - 2], x2[0, :n - 2]) and float(x1[0, n - 2:].abs().max()) == 0.0
+    # folded onto q through the mirrored API's difference operator: a directional finite difference of the total cost
+    q = torch.as_tensor(g["q"][None], device="cuda")
+    h = 1.0 / 120.0
+    F, par = torch.as_tensor(g["F"][None], device="cuda"), torch.as_tensor(par0[:1], device="cuda")
+
+    def total(qq):
+        dq_, ddq_ = kinetics.rates_from_q(qq, h)
+        e = kinetics.eom_rows(qq, dq_, ddq_, F, par)
+        return float((e * e).sum())
+
+    dq_, ddq_ = kinetics.rates_from_q(q, h)
+    _, a, b, c = kinetics.eom_vjp(q, dq_, ddq_, F, par)
+    grad = kinetics.states_gradient_to_q(a, b, c, h)
+    d = torch.as_tensor(rng.normal(size=tuple(q.shape)), device="cuda")
+    eps = 1e-7
+    fd = (total(q + eps * d) - total(q - eps * d)) / (2 * eps)
+    an = float((grad * d).sum())
+    assert abs(fd - an) <= 1e-5 * abs(an), (fd, an)
