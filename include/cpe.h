@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 120          /* 0.1.17 */
+#define CPE_VERSION 120          /* 0.1.20 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
