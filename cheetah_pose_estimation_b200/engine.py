@@ -188,7 +188,10 @@ class Batch:
                 return out
             assert bits == (self.meas_gate.dim() == 2)
             return self
-        uv = m[..., 0:2].to(torch.float32)
+        if m.dtype != torch.float32:
+            raise ValueError("Batch.compact: the compact layouts hold float32 coordinates; this batch keeps its detections in "
+                             "double (kinetic dataset) and would lose bits")
+        uv = m[..., 0:2]
         fin = ~torch.isnan(uv).any(dim=-1)                     # the device gate of the DLC-native layout (meas_unpack)
         gate = (m[..., 2].double() > float(self.dlc_thresh)) if m.shape[5] == 3 else (m[..., 2] != 0)
         gate = (gate & fin).to(torch.uint8).contiguous()

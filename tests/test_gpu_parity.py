@@ -377,6 +377,10 @@ def test_compact_layout_equals_dlc_native_and_pregated(gpu):
     o2, o3 = s2.evaluate(qd, resid=True, jac=True, f32=True), s3.evaluate(qd, resid=True, jac=True, f32=True)
     for k in ("cost", "resid", "jac"):
         assert torch.equal(o2[k], o3[k]), k
+    # double-precision detections (kinetic dataset) are not silently narrowed
+    b64 = engine.Batch.from_numpy(m4, prob.cams, prob.chain_vec, prob.h, meas_dtype=torch.float64)
+    with pytest.raises(ValueError, match="float32"):
+        b64.compact()
     # a compact batch without its gate array is refused at the boundary
     import ctypes as C
     from cheetah_pose_estimation_b200 import _lib
