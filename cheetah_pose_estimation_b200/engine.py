@@ -5,6 +5,7 @@ kinematic reconstruction: the arithmetic lives in libcpe_b200.so (include/cpe.h)
 memory (torch tensors), launches, and the few scalar decisions of the outer loop.
 """
 import ctypes as C
+import os
 from dataclasses import dataclass
 
 import numpy as np
@@ -777,15 +778,16 @@ def solve_split(model, batch, q0, n_split=2, priors=None, **kw):
 class HostEvaluator:
     """Residual + Jacobian evaluation for callers that keep their data in HOST memory (the reference-facing call:
     what the L4 shim does once per LM iteration when q lives in numpy).  Sequences are streamed through the GPU
-    in waves of `wave` sequences on two streams with two staging sets, so the host->device copy of wave i+1
-    overlaps the kernel of wave i.  Per wave it calls `cpe_eval_host_f64` (include/cpe.h): H2D of q and the
+    in waves of `wave` sequences on `n_streams` (default 4) streams with as many staging sets, so the host->device copies
+    of the next waves overlap the kernel of wave i (measured, detections resident: 471 / 557 / 613 M frame.views/s with
+    2 / 3 / 4 sets; the cold call is PCIe-bound and does not care).  Per wave it calls `cpe_eval_host_f64` (include/cpe.h): H2D of q and the
     detections, K1 with the chain-sparse Jacobian written to a device buffer, the per-sequence cost reduction,
     and D2H of cost[S,4].  Modes:
       resident_meas=True  the detections stay on the device (they are constant across the iterations of a solve) and
                           only q crosses the bus -- what one LM iteration of a host-side caller moves;
       resid_out=True      the residuals (`meas_err`, the array the reference saves: acinoset_opt.py:318) come back too."""
 
-    def __init__(self, model: Model, proto: Batch, S, wave, jac=True, resident_meas=False, resid_out=False):
+    def __init__(self, model: Model, proto: Batch, S, wave, jac=True, resident_meas=False, resid_out=False, n_streams=None):
         self.m, self.lib, self.proto = model, model.lib, proto
         self.S, self.wave, self.N, self.C, self.W = S, wave, proto.N, proto.C, proto.W
         self.resident_meas, self.resid_out = resident_meas, resid_out
@@ -794,9 +796,12 @@ class HostEvaluator:
         self.gate_bytes = (self.N * self.C * 24 * self.W // (8 if self.bits else 1)) if self.compact else 0   # per sequence
         dev = model.device
         f64 = dict(dtype=torch.float64, device=dev)
-        self.streams = [torch.cuda.Stream(device=dev) for _ in range(2)]
+        # staging sets = streams: with two, the copy of wave i + 2 waits for the kernel of wave i (same stream); a third set
+        # lets the copy engine run ahead, which matters when the kernel, not the copy, is the longer leg (resident_meas)
+        self.n_streams = int(n_streams or os.environ.get("CPE_HOST_STREAMS", 4))
+        self.streams = [torch.cuda.Stream(device=dev) for _ in range(self.n_streams)]
         self.stage = []
-        for _ in range(2):
+        for _ in range(self.n_streams):
             st = dict(q=torch.empty(wave, self.N, 54, **f64),
                       meas=None if resident_meas else torch.empty(wave, self.N, self.C, 24, self.W, proto.meas.shape[5],
                                                                   dtype=proto.meas.dtype, device=dev),
@@ -831,7 +836,7 @@ class HostEvaluator:
             st.wait_stream(cur)
         for i, s0 in enumerate(range(0, self.S, self.wave)):
             s1 = min(self.S, s0 + self.wave)
-            stg, stream = self.stage[i & 1], self.streams[i & 1]
+            stg, stream = self.stage[i % self.n_streams], self.streams[i % self.n_streams]
             bw = self.proto.window(s0, s1)
             bs = bw.struct()
             eo = _lib.CpeEvalOut()
