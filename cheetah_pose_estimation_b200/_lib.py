@@ -54,7 +54,7 @@ class CpeEvalOutF32(C.Structure):
 
 class CpeAssembleOut(C.Structure):
     _fields_ = [("S", c_f64p), ("ghat", c_f64p), ("Y", c_f64p), ("y", c_f64p), ("g", c_f64p), ("diagH", c_f64p),
-                ("Hraw", c_f64p), ("cam_blocks", c_f64p)]
+                ("Hraw", c_f64p), ("cam_blocks", c_f64p), ("ent", c_f64p), ("redamp", c_f64p)]
 
 
 class CpePrior(C.Structure):

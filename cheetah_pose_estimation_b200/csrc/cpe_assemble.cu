@@ -51,6 +51,7 @@ constexpr int A_QO = 0, A_POSO = 56, A_GV = 128, A_BV = 798, A_EQG = 1746, A_EQX
 static_assert(A_EQR - A_EQX == 156 && A_VIN - A_ACT == 32, "gradient entries read 156 / 32 doubles behind the Hessian ones");
 constexpr int K2_OFF_BLK = 41, K2_OFF_END = 45, K2_BLK_SLOTS = 8;      // must match skeleton.py
 constexpr int G_U0 = 10, B_U0 = 216, B_G0 = 876, GRAD_Q = 63;       // must match skeleton.py
+static_assert(CPE_K2_ENT_STORE >= 640 + 54, "ent record holds the entries and the diagonal");
 constexpr int ENT_PAD = 640, DDI_SZ = CPE_MAX_GROUPS * 72, YS_SZ = CPE_MAX_GROUPS * 78;
 
 __device__ __forceinline__ double motion_m0(int k, int nf) {
@@ -129,6 +130,14 @@ __global__ void __launch_bounds__(TEAM_T *NTEAM, 1) assemble_kernel(const __grid
     const size_t fidx = (size_t)f;
     const int ncam_s = p.b.n_cams ? p.b.n_cams[s] : C;      // cameras beyond it are padding of a ragged batch (weight 0)
     const size_t midx0 = ((fidx * C + mc) * 24 + ml) * W;
+    // A rejected LM step leaves q where it was: every entry of the frame Hessian and gradient is what the last full assembly
+    // computed.  Only the damping changed, and it enters behind the gather (elimination pivots, diagonal of S).
+    const bool redamp = p.ao.ent && p.ao.redamp && p.ao.redamp[s] < 0.0;
+    if (redamp) {
+        const double *src = p.ao.ent + fidx * CPE_K2_ENT_STORE;
+        for (int i = tid; i < ENT_PAD; i += nt) ENT[i] = src[i];
+        if (tid < 54) fr[A_DIAG + tid] = src[ENT_PAD + tid];
+    } else {
     if (tid < 54) fr[A_QO + tid] = q_cur;
     if (s != s_cam) {                                    // consecutive frames of a team mostly share the sequence
         for (int i = tid; i < C * CPE_CAM_STRIDE; i += nt) cam[i] = p.b.cams[(size_t)s * C * CPE_CAM_STRIDE + i];
@@ -375,7 +384,13 @@ __global__ void __launch_bounds__(TEAM_T *NTEAM, 1) assemble_kernel(const __grid
         const double d = ENT[p.m.diag_ent[tid]] + motion_m0(k, nf) * 2.0 * p.m.wq[tid] / h4;
         fr[A_DIAG + tid] = d;
         if (p.ao.diagH) p.ao.diagH[fidx * 54 + tid] = d;
+        if (p.ao.ent) p.ao.ent[fidx * CPE_K2_ENT_STORE + ENT_PAD + tid] = d;
     }
+    if (p.ao.ent) {
+        double *dst = p.ao.ent + fidx * CPE_K2_ENT_STORE;
+        for (int i = tid; i < ENT_PAD; i += nt) dst[i] = ENT[i];
+    }
+    }   // full assembly
     if (!p.ao.S) { team_sync<TEAM_T>(team); continue; }
     team_sync<TEAM_T>(team);
 
@@ -482,6 +497,7 @@ extern "C" int cpe_assemble_f64(const cpe_model *model, const cpe_batch *b, cons
     if (model->n_u != 198 || model->n_ent <= 0 || model->n_ent > ENT_PAD) return CPE_E_DIM;
     if (!model->k2_tab || !model->diag_ent || !model->grp_dep || !model->ind_idx) return CPE_E_NULL;
     if (out->S && (!damp || !out->ghat || !out->Y || !out->y)) return CPE_E_NULL;
+    if (out->redamp && (!out->ent || !out->S)) return CPE_E_NULL;
     if ((b->shutter_tau || b->base_dq || b->base_ddq) && !(b->shutter_tau && b->base_dq && b->base_ddq)) return CPE_E_NULL;
     AsmParams p;
     p.m = *model; p.b = *b; p.q = q; p.damp = damp; p.ao = *out;

@@ -229,9 +229,14 @@ class Batch:
 class Solver:
     """Workspaces + launches for one (model, batch)."""
 
-    def __init__(self, model: Model, batch: Batch, with_solver=True, priors=None):
-        """priors: a `priors.Priors` (monocular data-driven terms) or None."""
+    def __init__(self, model: Model, batch: Batch, with_solver=True, priors=None, redamp=True):
+        """priors: a `priors.Priors` (monocular data-driven terms) or None.
+        redamp: after a REJECTED LM step q is unchanged, so K2 only re-damps the stored undamped entries
+        (cpe_assemble_out.ent / redamp) instead of assembling the frame again -- bit-identical results; plain multi-view
+        solves only (the prior and shutter-delay paths add to g / diagH in place after K2 and keep assembling in full)."""
         self.m, self.b = model, batch
+        self._redamp = bool(redamp) and with_solver and priors is None
+        self._redamp_on = False
         self.lib = model.lib
         self.priors = priors
         S, N, dev = batch.S, batch.N, model.device
@@ -269,6 +274,7 @@ class Solver:
             self.q_try = torch.zeros(S, N, 54, **f64)
             self.frame_pred = torch.zeros(S, N, **f64)
             self.state = torch.zeros(4, S, **f64)
+            self.ent = torch.zeros(S, N, 704, **f64) if self._redamp else None       # CPE_K2_ENT_STORE
             self.counters = torch.zeros(S, 2, dtype=torch.int32, device=dev)
             self.active = torch.ones(S, dtype=torch.int32, device=dev)
             self.c_eq = torch.zeros(S, N, 26, **f64)
@@ -356,6 +362,10 @@ class Solver:
             ao.cam_blocks = self.cam_blocks.data_ptr()
         if raw is not None:
             ao.Hraw = raw.data_ptr()
+        if reduced and self._redamp:
+            ao.ent = self.ent.data_ptr()
+            if self._redamp_on:                      # inside solve_steps: row 3 of `state` is -1 where the last step was rejected
+                ao.redamp = self.state[3].data_ptr()
         return ao
 
     def assemble(self, q, damp, raw=False, reduced=True):
@@ -489,6 +499,8 @@ class Solver:
             ftol = float(ftols[min(outer, len(ftols) - 1)])      # inexact inner solves while the multipliers are rough
             self.evaluate(q)
             self.state[0].copy_(self.cost.sum(dim=1))
+            self.state[3].zero_()                    # new penalty / multipliers: the first assembly of a round is a full one
+            self._redamp_on = self._redamp
             if self.priors is not None:
                 self.state[0].add_(self.prior_cost.sum(dim=1))
             if need is None:
@@ -559,6 +571,7 @@ class Solver:
                                                       _ptr(b.lam_eq), _ptr(b.lam_in), _stream()),
                        "cpe_update_multipliers_f64")
             self.launches += 1
+        self._redamp_on = False
         if held is not None:
             # sequences that sat out the extra rounds keep the activity (= MAXITER) flag of their own last round
             self.active.copy_(torch.where(ever != 0, self.active, held))

@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define CPE_VERSION 120          /* 0.1.20 */
+#define CPE_VERSION 121          /* 0.1.21 */
 
 #define CPE_N_MARKERS 24
 #define CPE_N_LINKS 17
@@ -210,6 +210,14 @@ typedef struct cpe_assemble_out {
                                        IRLS-weighted P^T P (xx, xy, xz, yy, yz, zz) and P^T rho' (x, y, z), P = d(u,v)/d(point).
                                        The shutter-delay terms are built from these: d cost / d tau_c =
                                        sum_n b_nc . (dq_base + 2 tau_c ddq_base), and the gradient through dq_base, ddq_base */
+    double *ent;                    /* optional [S,N,CPE_K2_ENT_STORE]: the UNDAMPED Hessian / gradient entries of the frame (the
+                                       gather results, cpe_model.n_ent <= 640 values) followed at 640 by diagH[54]; written by
+                                       every full assembly, read back by a re-damp (next field) */
+    const double *redamp;           /* optional [S], needs `ent`: sequences with redamp[s] < 0 only RE-DAMP -- their q has not
+                                       changed since the last call (a rejected LM step: cpe_step_accept leaves -1 in row 3 of
+                                       its `state`), so the entries are read back from `ent` and only the damped elimination
+                                       and the Schur gather run again.  S, ghat, Y, y come out bit-identical to a full
+                                       assembly; g, diagH, Hraw, cam_blocks are left as the last full assembly wrote them */
 } cpe_assemble_out;
 
 /* Data-driven monocular priors on the reduced pose x = Tr q_ind (28 = the coordinates with a motion prior; the
@@ -383,6 +391,7 @@ int cpe_eom_vjp_f64(const cpe_batch *batch, const double *q, const double *dq, c
  * Calls no cudaMalloc / cudaFree / allocating routine; results are bit-identical to cpe_eom_slack_f64.
  * EVERY call on a device shares that one array (the part a call uses is cleared first, on `stream`): calls that overlap
  * on the GPU -- different streams, or graphs replayed concurrently -- RACE; serialise them. */
+#define CPE_K2_ENT_STORE 704       /* doubles per frame of cpe_assemble_out.ent: 640 entries + diagH[54], padded */
 #define CPE_NOALLOC_MAX_FRAMES 65536
 int cpe_eom_slack_noalloc_f64(const cpe_batch *batch, const double *eom, const double *Bm, double *cost, double *grad_f,
                               void *stream);

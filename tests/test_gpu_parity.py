@@ -694,3 +694,45 @@ def test_extra_rounds_only_touch_sequences_that_are_not_yet_feasible(gpu):
     sv2 = engine.Solver(gpu, prob.to_batch("cuda:0"))
     res2 = sv2.solve(q0, extra_outer=6, feas_tol=(1.0, 1.0), **kw)
     assert sv2.extra_rounds == 0 and all(torch.equal(res2[k], base[k]) for k in ("q", "cost", "status"))
+
+
+def test_redamp_after_a_rejected_step_equals_a_full_assembly(gpu):
+    """cpe_assemble_out.ent / redamp: K2 keeps the undamped entries of every frame; for sequences flagged as rejected it
+    reads them back and only repeats the damped elimination and the Schur gather.  (i) at the kernel level the re-damped
+    S, ghat, Y, y equal a full assembly at the new damping bit for bit, flagged and unflagged sequences alike; (ii) a
+    whole solve with the shortcut equals the solve without it bit for bit, on a problem whose LM loop does reject steps."""
+    import torch
+    from cheetah_pose_estimation_b200 import engine, synthetic
+    prob, batch, solver, q, qd = _setup(gpu, S=4, N=10, C=6, seed=71)
+    rng = np.random.default_rng(9)
+    batch.lam_eq = torch.as_tensor(rng.normal(0, 3, (4, 10, 26)), device="cuda:0")
+    batch.lam_in = torch.as_tensor(rng.normal(0, 3, (4, 10, gpu.n_ineq)), device="cuda:0")
+    f64 = dict(dtype=torch.float64, device="cuda:0")
+    d0 = torch.full((4,), 1e-3, **f64)
+    d1 = torch.tensor([1e-3, 7e-2, 1e-3, 3.0], **f64)                      # sequences 1 and 3 were "rejected": new damping
+    solver.assemble(qd, d0)                                                # full: fills ent
+    assert float(solver.ent.abs().max()) > 0
+    solver.state[3].copy_(torch.tensor([0.5, -1.0, 0.0, -1.0], **f64))
+    solver._redamp_on = True
+    solver.assemble(qd, d1)                                                # 1 and 3 re-damp, 0 and 2 assemble in full
+    solver._redamp_on = False
+    got = {k: getattr(solver, k).clone() for k in ("Sblk", "ghat", "Y", "y", "g", "diagH")}
+    ref = engine.Solver(gpu, batch, redamp=False)
+    ref.assemble(qd, d1)
+    for k in got:
+        assert torch.equal(got[k], getattr(ref, k)), k
+    assert not torch.equal(got["Sblk"][1], engine.Solver(gpu, batch, redamp=False).Sblk[1])      # (and it is not all zeros)
+    # (ii) whole solves
+    prob2 = synthetic.make_problem(S=5, N=14, C=4, seed=52)
+    prob2.n_frames[:] = (14, 9, 14, 4, 11)
+    q0 = torch.as_tensor(prob2.q_init, device="cuda:0")
+    a = engine.Solver(gpu, prob2.to_batch("cuda:0"), redamp=False).solve(q0, max_iter=15, n_outer=3)
+    sb = engine.Solver(gpu, prob2.to_batch("cuda:0"))
+    assert sb._redamp and sb.ent is not None
+    b = sb.solve(q0, max_iter=15, n_outer=3)
+    assert bool((a["counters"][:, 0] > a["counters"][:, 1]).any()), "no rejected step: the test does not exercise the path"
+    for k in ("q", "cost", "counters", "status", "c_eq", "v_in"):
+        assert torch.equal(a[k], b[k]), k
+    # with the iteration captured in a CUDA graph as well
+    c = engine.Solver(gpu, prob2.to_batch("cuda:0")).solve(q0, max_iter=15, n_outer=3, graph=True)
+    assert torch.equal(a["q"], c["q"]) and torch.equal(a["counters"], c["counters"])
