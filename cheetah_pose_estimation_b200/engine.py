@@ -235,7 +235,7 @@ class Solver:
         (cpe_assemble_out.ent / redamp) instead of assembling the frame again -- bit-identical results; plain multi-view
         solves only (the prior and shutter-delay paths add to g / diagH in place after K2 and keep assembling in full)."""
         self.m, self.b = model, batch
-        self._redamp = bool(redamp) and with_solver and priors is None
+        self._redamp = bool(redamp) and with_solver and priors is None and os.environ.get("CPE_REDAMP", "1") != "0"
         self._redamp_on = False
         self.lib = model.lib
         self.priors = priors
