@@ -233,7 +233,8 @@ class Solver:
         """priors: a `priors.Priors` (monocular data-driven terms) or None.
         redamp: after a REJECTED LM step q is unchanged, so K2 only re-damps the stored undamped entries
         (cpe_assemble_out.ent / redamp) instead of assembling the frame again -- bit-identical results; plain multi-view
-        solves only (the prior and shutter-delay paths add to g / diagH in place after K2 and keep assembling in full)."""
+        solves only (the prior and shutter-delay paths add to g / diagH in place after K2 and keep assembling in full).
+        Environment CPE_REDAMP=0 switches it off for A/B timing (profiles/r2w_redamp_ab.txt)."""
         self.m, self.b = model, batch
         self._redamp = bool(redamp) and with_solver and priors is None and os.environ.get("CPE_REDAMP", "1") != "0"
         self._redamp_on = False
