@@ -117,6 +117,9 @@ class CpeError(RuntimeError):
     pass
 
 
+ABI_VERSION = 121          # CPE_VERSION of include/cpe.h the ctypes mirrors were written for (tests/test_abi.py)
+
+
 def load():
     """Load libcpe_b200.so and type its entry points.  Raises if the library is absent (no CPU fallback)."""
     global _lib
@@ -130,6 +133,10 @@ def load():
         fn = getattr(lib, name)          # AttributeError if the symbol is missing
         fn.restype = res
         fn.argtypes = args
+    if lib.cpe_version() != ABI_VERSION:
+        # the struct mirrors above are laid out for exactly this header version: a stale .so would read fields at wrong offsets
+        raise CpeError(f"{LIB_PATH} is ABI version {lib.cpe_version()}, this package mirrors {ABI_VERSION} (include/cpe.h): "
+                       "rebuild with `python -c 'import __graft_entry__ as g; g.build()'`")
     _lib = lib
     return lib
 

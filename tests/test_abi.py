@@ -24,7 +24,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), n
     assert sorted(_lib.EXPORTS) == names
-    assert lib.cpe_version() == 121
+    assert lib.cpe_version() == 121 == _lib.ABI_VERSION
 
 
 def test_struct_mirrors_match_header_field_order():
