@@ -25,6 +25,8 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(lib, n), n
     assert sorted(_lib.EXPORTS) == names
     assert lib.cpe_version() == 121 == _lib.ABI_VERSION
+    hdr = open(os.path.join(ROOT, "include", "cpe.h")).read()
+    assert int(re.search(r"#define CPE_VERSION (\d+)", hdr).group(1)) == _lib.ABI_VERSION
 
 
 def test_struct_mirrors_match_header_field_order():
