@@ -58,6 +58,9 @@ def parse_args():
     ap.add_argument("--shutter-seqs", type=int, default=148, help="sequences of the shutter-delay leg (0 = skip)")
     ap.add_argument("--cpu-seqs", type=int, default=64, help="sequences of the cpu_baseline sample (0 = skip)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-wave", type=int, default=128,
+                    help="sequences per wave of the end-to-end legs (engine.HostEvaluator): smaller waves shorten the part of a "
+                         "step that cannot overlap, the first copy and the last kernel")
     ap.add_argument("--no-f32", action="store_true", help="skip the FP32-flavour leg")
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--unique", type=int, default=4096,
@@ -341,7 +344,7 @@ def run_b200(a):
         e2e = {"host_pack_ms_once": pack_ms}
         for mode in ("cold", "dlc", "resident", "cold_resid"):
             proto = batch if mode == "dlc" else cbatch
-            hev = engine.HostEvaluator(model, proto, S, wave, resident_meas=(mode == "resident"),
+            hev = engine.HostEvaluator(model, proto, S, min(a.e2e_wave, S), resident_meas=(mode == "resident"),
                                        resid_out=(mode == "cold_resid"))
             args = (h_q,) if mode == "resident" else ((h_q, h_meas) if mode == "dlc" else (h_q, h_uv, h_gate))
             for _ in range(max(1, min(a.warmup, 3)) if mode == "cold" else 1):
