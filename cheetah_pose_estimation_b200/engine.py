@@ -752,6 +752,9 @@ def shutter_jacobian(jac, batch):
     return torch.einsum("snclid,snci->sncld", P, d)
 
 
+_SPLIT_STREAMS = {}
+
+
 def solve_split(model, batch, q0, n_split=2, priors=None, **kw):
     """LM-solve `batch` as `n_split` independent sub-batches on their own CUDA streams, launches interleaved from one
     host thread.  The block-banded solve K3 is a latency-bound sweep along time (one CTA per sequence, ~10 % issue
@@ -761,14 +764,20 @@ def solve_split(model, batch, q0, n_split=2, priors=None, **kw):
     n_split = max(1, min(n_split, S))
     cuts = [S * i // n_split for i in range(n_split + 1)]
     cur = torch.cuda.current_stream()
-    streams = [torch.cuda.Stream(device=model.device) for _ in range(n_split)]
+    # the same stream objects from call to call: torch's caching allocator keeps its free blocks PER STREAM, so fresh streams
+    # would make every call cudaMalloc its ~40 GB of workspaces anew (measured: 23 cudaMalloc calls / 32 GB inside a solve)
+    key = (str(model.device), n_split)
+    if key not in _SPLIT_STREAMS:
+        _SPLIT_STREAMS[key] = ([torch.cuda.Stream(device=model.device) for _ in range(n_split)],
+                               [torch.cuda.Stream(device=model.device, priority=-1) for _ in range(n_split)])
+    streams, k3_streams = _SPLIT_STREAMS[key]
     solvers, gens = [], []
     for i, st in enumerate(streams):
         st.wait_stream(cur)
         with torch.cuda.stream(st):
             sv = Solver(model, batch.window(cuts[i], cuts[i + 1]), priors=priors)
             if n_split > 1:
-                sv.k3_stream = torch.cuda.Stream(device=model.device, priority=-1)
+                sv.k3_stream = k3_streams[i]
             solvers.append(sv)
             gens.append(sv.solve_steps(q0[cuts[i]:cuts[i + 1]].contiguous(), **kw))
     live = list(range(n_split))
